@@ -1,0 +1,224 @@
+"""CPU tests: pin the oracle (oracle/*.h, the CPU restatement of the reference's
+ITERATIVE_SCHUR path) against the reference's own known-answer fixtures
+(tests/golden/kat_problems.py, transcribed from linear_least_squares_problems.cc)
+and against the identities the reference's tests assert:
+  partitioned_matrix_view_test.cc:103-230, implicit_schur_complement_test.cc:55-237,
+  iterative_schur_complement_solver_test.cc:60-149, schur_eliminator_test.cc,
+  conjugate_gradients_solver_test.cc:47-160,
+  power_series_expansion_preconditioner_test.cc:85-173.
+"""
+import numpy as np
+import pytest
+
+from oracle import binding as ob
+from tests.golden import kat_problems as kp
+
+
+def make(pid, **kw):
+    st_kw, values, b, D, extra = kp.flat(pid)
+    st = ob.Structure(**st_kw)
+    return st, values, b, D, extra, ob.Oracle(st, **kw)
+
+
+def dense_solution(A, b, D):
+    H = A.T @ A + (np.diag(D * D) if D is not None else 0)
+    return np.linalg.solve(H, A.T @ b)
+
+
+def dense_schur(A, D, ne):
+    H = A.T @ A + (np.diag(D * D) if D is not None else 0)
+    Hee, Hef, Hff = H[:ne, :ne], H[:ne, ne:], H[ne:, ne:]
+    return Hff - Hef.T @ np.linalg.solve(Hee, Hef)
+
+
+@pytest.mark.parametrize("pid", [2, 4, 5, 6])
+@pytest.mark.parametrize("threads", [1, 2, 4, 8])
+def test_partitioned_view_products(pid, threads):
+    st, values, b, D, _, o = make(pid, num_threads=threads)
+    A = st.dense(values)
+    ne = st.num_cols_e
+    rng = np.random.default_rng(pid)
+    xe, xf = rng.standard_normal(ne), rng.standard_normal(st.num_cols_f)
+    xr = rng.standard_normal(st.num_rows)
+    y = np.zeros(st.num_rows); o.pmv(values, 0, xe, y)
+    np.testing.assert_allclose(y, A[:, :ne] @ xe, atol=1e-14)
+    y = np.zeros(st.num_rows); o.pmv(values, 1, xf, y)
+    np.testing.assert_allclose(y, A[:, ne:] @ xf, atol=1e-14)
+    y = np.zeros(ne); o.pmv(values, 2, xr, y)
+    np.testing.assert_allclose(y, A[:, :ne].T @ xr, atol=1e-14)
+    y = np.zeros(st.num_cols_f); o.pmv(values, 3, xr, y)
+    np.testing.assert_allclose(y, A[:, ne:].T @ xr, atol=1e-14)
+
+
+@pytest.mark.parametrize("pid", [2, 4, 5, 6])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_block_diagonals(pid, threads):
+    st, values, b, D, _, o = make(pid, num_threads=threads)
+    A = st.dense(values)
+    for which, lo, hi in [(0, 0, st.num_eliminate_blocks),
+                          (1, st.num_eliminate_blocks, len(st.col_size))]:
+        got = o.block_diagonal(values, which)
+        H = A.T @ A
+        k = 0
+        for cbi in range(lo, hi):
+            s, p = st.col_size[cbi], st.col_pos[cbi]
+            np.testing.assert_allclose(got[k:k + s * s].reshape(s, s),
+                                       H[p:p + s, p:p + s], atol=1e-14)
+            k += s * s
+        assert k == len(got)
+
+
+@pytest.mark.parametrize("pid", [2, 4, 5, 6])
+@pytest.mark.parametrize("use_D", [False, True])
+@pytest.mark.parametrize("threads", [1, 3])
+def test_implicit_schur_complement(pid, use_D, threads):
+    if pid in (4, 6) and not use_D:
+        pytest.skip("rank deficient without regularisation (reference note :543)")
+    st, values, b, D, _, o = make(pid, num_threads=threads,
+                                  preconditioner_type=ob.JACOBI)
+    Dv = D if use_D else None
+    A = st.dense(values)
+    ne, nf = st.num_cols_e, st.num_cols_f
+    S = dense_schur(A, Dv, ne)
+    H = A.T @ A + (np.diag(D * D) if use_D else 0)
+    g = A.T @ b
+    rhs = g[ne:] - H[:ne, ne:].T @ np.linalg.solve(H[:ne, :ne], g[:ne])
+    o.isc_init(values, Dv, b)
+    scale = max(1.0, np.abs(S).max())
+    for i in range(nf):
+        e = np.zeros(nf); e[i] = 1.0
+        np.testing.assert_allclose(o.isc_multiply(e), S[:, i], atol=1e-12 * scale)
+    np.testing.assert_allclose(o.isc_rhs(), rhs, atol=1e-12 * max(1, np.abs(rhs).max()))
+    z = np.linalg.solve(S, rhs)
+    sol = dense_solution(A, b, Dv)
+    np.testing.assert_allclose(o.isc_back_substitute(z), sol, atol=1e-12)
+    # InversePowerSeriesOperator == (F'F)^-1 F'E (E'E)^-1 E'F
+    Z = np.linalg.solve(H[ne:, ne:] * 0 + _blockdiag(H[ne:, ne:], st), H[ne:, ne:] * 0 +
+                        H[:ne, ne:].T @ np.linalg.solve(_blockdiag_e(H[:ne, :ne], st), H[:ne, ne:]))
+    for i in range(nf):
+        e = np.zeros(nf); e[i] = 1.0
+        np.testing.assert_allclose(o.isc_pse_operator(e, np.zeros(nf)), Z[:, i],
+                                   atol=1e-12)
+
+
+def _blockdiag(Hff, st):
+    out = np.zeros_like(Hff)
+    base = st.num_cols_e
+    for cbi in range(st.num_eliminate_blocks, len(st.col_size)):
+        s, p = st.col_size[cbi], st.col_pos[cbi] - base
+        out[p:p + s, p:p + s] = Hff[p:p + s, p:p + s]
+    return out
+
+
+def _blockdiag_e(Hee, st):
+    out = np.zeros_like(Hee)
+    for cbi in range(st.num_eliminate_blocks):
+        s, p = st.col_size[cbi], st.col_pos[cbi]
+        out[p:p + s, p:p + s] = Hee[p:p + s, p:p + s]
+    return out
+
+
+def test_problem2_published_solution():
+    """linear_least_squares_problems.cc:311-316 gives x = A\\b to 4 decimals
+    (the unregularised solution, D = nullptr)."""
+    st, values, b, D, extra, o = make(2, max_num_iterations=5)
+    x, s = o.solve(values, b, None, r_tolerance=1e-12)
+    assert ob.TERMINATION[s["termination_type"]] == "SUCCESS"
+    np.testing.assert_allclose(x, extra["x"], atol=5e-5)
+
+
+def test_problem5_published_schur_complement():
+    """:628-676 gives S, r and S\\r (no regularisation) to 4 decimals."""
+    st, values, b, D, extra, o = make(5, preconditioner_type=ob.JACOBI)
+    o.isc_init(values, None, b)
+    nf = st.num_cols_f
+    S = np.stack([o.isc_multiply(np.eye(nf)[i]) for i in range(nf)], axis=1)
+    np.testing.assert_allclose(S, extra["S"], atol=5e-5)
+    np.testing.assert_allclose(o.isc_rhs(), extra["r"], atol=5e-5)
+    np.testing.assert_allclose(np.linalg.solve(S, o.isc_rhs()), extra["S_solve_r"],
+                               atol=5e-5)
+
+
+# iterative_schur_complement_solver_test.cc:125-149
+@pytest.mark.parametrize("pid,ptype,spse_init", [
+    (2, ob.SCHUR_JACOBI, False), (2, ob.SCHUR_JACOBI, True),
+    (5, ob.SCHUR_POWER_SERIES_EXPANSION, False), (3, ob.SCHUR_JACOBI, False),
+    (2, ob.JACOBI, False), (2, ob.IDENTITY, False)])
+@pytest.mark.parametrize("use_D", [False, True])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_iterative_schur_solver_vs_dense(pid, ptype, spse_init, use_D, threads):
+    st, values, b, D, _, o = make(
+        pid, num_threads=threads, preconditioner_type=ptype,
+        max_num_iterations=st_cols(pid), max_num_spse_iterations=1,
+        use_spse_initialization=spse_init)
+    Dv = D if use_D else None
+    x, s = o.solve(values, b, Dv, q_tolerance=0.0, r_tolerance=1e-12)
+    ref = dense_solution(st.dense(values), b, Dv)
+    assert np.linalg.norm(x - ref) < 1e-13 * max(1.0, np.linalg.norm(ref)), s
+
+
+def st_cols(pid):
+    return sum(c[0] for c in kp.PROBLEMS[pid]["cols"])
+
+
+@pytest.mark.parametrize("pid", [2, 4, 5, 6])
+@pytest.mark.parametrize("use_D", [False, True])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_schur_jacobi_blocks(pid, use_D, threads):
+    if pid in (4, 6) and not use_D:
+        pytest.skip("rank deficient without regularisation")
+    st, values, b, D, _, o = make(pid, num_threads=threads)
+    Dv = D if use_D else None
+    S = dense_schur(st.dense(values), Dv, st.num_cols_e)
+    got = o.schur_jacobi(values, Dv, invert=False)
+    inv = o.schur_jacobi(values, Dv, invert=True)
+    k, base = 0, st.num_cols_e
+    for cbi in range(st.num_eliminate_blocks, len(st.col_size)):
+        s, p = st.col_size[cbi], st.col_pos[cbi] - base
+        blk = S[p:p + s, p:p + s]
+        np.testing.assert_allclose(got[k:k + s * s].reshape(s, s), blk,
+                                   rtol=1e-12, atol=1e-12 * np.abs(blk).max())
+        np.testing.assert_allclose(inv[k:k + s * s].reshape(s, s), np.linalg.inv(blk),
+                                   rtol=1e-10, atol=1e-12)
+        k += s * s
+
+
+def test_power_series_converges_to_inverse():
+    """power_series_expansion_preconditioner_test.cc:85-128: on problem 5 (F'F is
+    block diagonal) enough series terms reproduce S^-1."""
+    st, values, b, D, _, o = make(5, preconditioner_type=ob.SCHUR_POWER_SERIES_EXPANSION)
+    o.isc_init(values, D, b)
+    S = dense_schur(st.dense(values), D, st.num_cols_e)
+    nf = st.num_cols_f
+    for i in range(nf):
+        y = o.pse_apply(np.eye(nf)[i], 100, 1e-30)
+        np.testing.assert_allclose(y, np.linalg.inv(S)[:, i], atol=1e-12)
+    # one term only is NOT the inverse (:130-173)
+    y = o.pse_apply(np.eye(nf)[0], 1, 1e-30)
+    assert np.abs(y - np.linalg.inv(S)[:, 0]).max() > 1e-4
+
+
+def test_cg_identity_and_tridiagonal():
+    """conjugate_gradients_solver_test.cc:47-160."""
+    x, s = ob.cg_dense(np.eye(3), [1, 2, 3], [1, 1, 1], 1, 10, 20, 0.0, 1e-9)
+    assert ob.TERMINATION[s["termination_type"]] == "SUCCESS"
+    assert s["num_iterations"] == 1
+    np.testing.assert_allclose(x, [1, 2, 3], rtol=4e-16)
+    A = [[2, -1, 0], [-1, 2, -1], [0, -1, 2]]
+    x, s = ob.cg_dense(A, [-1, 0, 3], [1, 1, 1], 1, 10, 20, 0.0, 1e-9)
+    assert ob.TERMINATION[s["termination_type"]] == "SUCCESS"
+    np.testing.assert_allclose(x, [0, 1, 2], atol=1e-14)
+
+
+def test_llt_inverse_uses_upper_triangle_only():
+    rng = np.random.default_rng(0)
+    for n in (1, 2, 3, 9):
+        M = rng.standard_normal((n + 3, n))
+        A = M.T @ M + np.eye(n)
+        m = np.triu(A) + np.tril(rng.standard_normal((n, n)), -1)  # garbage below
+        m = np.ascontiguousarray(m)
+        ob.lib().oracle_llt_inverse_upper(ob._dp(m), n)
+        np.testing.assert_allclose(m, np.linalg.inv(A), rtol=1e-11, atol=1e-13)
+        out = np.zeros((n, n))
+        ob.lib().oracle_inverse_small(ob._dp(np.ascontiguousarray(A)), n, ob._dp(out))
+        np.testing.assert_allclose(out, np.linalg.inv(A), rtol=1e-11, atol=1e-13)
