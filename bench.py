@@ -1,0 +1,276 @@
+#!/usr/bin/env python
+"""bench.py — ITERATIVE_SCHUR linear solves per second on a synthetic Venice-shape BAL problem.
+
+A step = the linear solve of one Levenberg-Marquardt iteration (ImplicitSchurComplement::Init,
+SCHUR_JACOBI update, PCG to q_tolerance = eta = 1e-2, back substitution) on the Jacobi-scaled
+Snavely Jacobian of the problem, exactly what LevenbergMarquardtStrategy::ComputeStep hands to
+LinearSolver::Solve. `value` is measured with values / b / D resident in HBM; `e2e` goes through
+cb200_solve with pinned HOST buffers (H2D of J, b, D and D2H of x inside the timed region).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--shape venice]
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "ceres-solver-ceres-solver_b200"
+ETA = 1e-2            # bundle_adjuster.cc:114
+MAX_PCG = 500         # bundle_adjuster.cc:120
+RADIUS = 1e4          # Solver::Options::initial_trust_region_radius
+
+
+def make_problem(shape, scale):
+    pkg = importlib.import_module(PKG)
+    p = pkg.SyntheticBAL.named(shape, scale=scale, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    cost, residuals, values = p.evaluate()
+    jscale = 1.0 / (1.0 + np.sqrt(p.squared_column_norm(values)))  # trust_region_minimizer.cc:263-279
+    p.scale_columns(values, jscale)
+    D = np.sqrt(np.clip(p.squared_column_norm(values), 1e-6, 1e32) / RADIUS)  # lm_strategy.cc:79-95
+    return pkg, p, values, residuals, D
+
+
+def algorithmic_bytes_sx(N, P, C):
+    """J values once + camera ids + row starts + (E'E)^-1 blocks + x in / y out."""
+    return 192 * N + 4 * N + 4 * P + 72 * P + 2 * 72 * C
+
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(device), f"--query-gpu={self.FIELDS}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.f:
+            c = [t.strip() for t in line.split(",")]
+            if len(c) < 6:
+                continue
+            try:
+                sm.append(float(c[0])); mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.f.name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                   "samples": len(sm)}
+        return out
+
+
+def run_reference(args, rank):
+    """The reference's own CPU implementation of the path. The reference cannot be compiled here
+    (every translation unit of the path needs Eigen, absent from the image), so this arm times the
+    oracle port of it on the host cores, all threads."""
+    if rank != 0:
+        return
+    from oracle import binding as ob
+    pkg, p, values, residuals, D = make_problem(args.shape, args.scale)
+    st = p.structure
+    cores = os.cpu_count()
+    ost = ob.Structure(st.row_size, st.row_pos, st.cell_ptr, st.cell_block_id, st.cell_position, st.col_size,
+                       st.col_pos, st.num_eliminate_blocks)
+    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=MAX_PCG,
+                  native=True)
+    its = 0
+    for _ in range(args.warmup):
+        o.solve(values, residuals, D, ETA, -1.0)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _, s = o.solve(values, residuals, D, ETA, -1.0)
+        its += s["num_iterations"]
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    line = {"impl": "reference", "metric": "lm_linear_solves_per_sec", "value": v, "unit": "LM iters/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(args, p), "pcg_iterations_per_step": its / args.steps,
+            "pcg_iters_per_sec": its / dt,
+            "cpu_baseline": {"value": v, "unit": "LM iters/s", "cores": cores, "kind": "port",
+                             "sample": f"{args.steps} full solves of the same problem"},
+            "e2e": {"value": v, "unit": "LM iters/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, p):
+    return {"workload": f"synthetic BAL {args.shape}-shape x{args.scale:g}: {p.C} cameras, {p.P} points, "
+                        f"{p.N} observations; ITERATIVE_SCHUR + SCHUR_JACOBI, eta={ETA}, first LM iteration "
+                        f"(Jacobi-scaled Snavely Jacobian, radius {RADIUS:g})",
+            "cameras": p.C, "points": p.P, "observations": p.N,
+            "l2": "inputs (24*N doubles) exceed the 126 MB L2; no flush needed"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--shape", default="venice")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    uid = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pkg, p, values, residuals, D = make_problem(args.shape, args.scale)
+    if world > 1:
+        t = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            t = torch.frombuffer(bytearray(pkg.nccl_unique_id()), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        uid = bytes(t.cpu().numpy().tobytes())
+
+    def pinned(a):
+        t = torch.empty(a.shape, dtype=torch.float64, pin_memory=True)
+        t.numpy()[...] = a
+        return t
+
+    hv, hb, hD = pinned(values), pinned(residuals), pinned(D)
+    hx = torch.zeros(3 * p.P + 9 * p.C, dtype=torch.float64, pin_memory=True)
+    g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=pkg.SCHUR_JACOBI,
+                                           max_num_iterations=MAX_PCG, device_id=local_rank, rank=rank,
+                                           world_size=world, nccl_unique_id=uid)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- HBM-resident arm -----------------------------------------------------------------------
+    g.upload_ptr(hv.data_ptr(), hb.data_ptr(), hD.data_ptr())
+    for _ in range(args.warmup):
+        s = g.solve_resident(ETA, -1.0)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    dev_ms, its, launches = 0.0, 0, 0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        s = g.solve_resident(ETA, -1.0)
+        dev_ms += s["setup_ms"] + s["pcg_ms"] + s["back_substitute_ms"]
+        its += s["num_iterations"]
+        launches += s["kernel_launches"]
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clocks = sampler.stop() if sampler else None
+    dev_ms = max_over_ranks(dev_ms)
+    wall_ms = max_over_ranks(wall_ms)
+    phases = {k: s[k] for k in ("setup_ms", "pcg_ms", "back_substitute_ms")}
+
+    # ---- end to end through the C ABI with host buffers -------------------------------------------
+    for _ in range(2):
+        g.solve_ptr(hv.data_ptr(), hb.data_ptr(), hD.data_ptr(), ETA, -1.0, hx.data_ptr())
+    barrier()
+    e2e_ms = 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        s2 = g.solve_ptr(hv.data_ptr(), hb.data_ptr(), hD.data_ptr(), ETA, -1.0, hx.data_ptr())
+        e2e_ms += s2["h2d_ms"] + s2["setup_ms"] + s2["pcg_ms"] + s2["back_substitute_ms"] + s2["d2h_ms"]
+    barrier()
+    e2e_wall_ms = max_over_ranks(1e3 * (time.perf_counter() - t0))
+    e2e_ms = max_over_ranks(e2e_ms)
+    n_loc = g.row_end - g.row_begin
+    p_loc = g.point_end - g.point_begin
+    h2d = 8 * (24 * n_loc + 2 * n_loc + 3 * p_loc + 9 * p.C)
+    d2h = 8 * (3 * p_loc + 9 * p.C)
+
+    # ---- roofline of the dominant kernel (fused S*x), timed alone with CUDA events ----------------
+    sx_ms, _ = g.time_op(6, warmup=3, iters=20)
+    sx_ms = max_over_ranks(sx_ms)
+    bytes_sx = algorithmic_bytes_sx(n_loc, p_loc, p.C)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = bytes_sx / (sx_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "point_tile_kernel<kModeSx>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
+                "bytes_per_launch": bytes_sx, "ms_per_launch": sx_ms}
+
+    if rank == 0:
+        line = {"metric": "lm_linear_solves_per_sec", "value": args.steps / (dev_ms * 1e-3), "unit": "LM iters/s",
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": workload_config(args, p),
+                "pcg_iterations_per_step": its / args.steps, "pcg_iters_per_sec": its / (dev_ms * 1e-3),
+                "wall_ms_per_step": wall_ms / args.steps, "phases_ms_last_step": phases,
+                "termination": s["message"],
+                "e2e": {"value": args.steps / (e2e_ms * 1e-3), "unit": "LM iters/s", "h2d_bytes_per_step": h2d,
+                        "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps,
+                        "wall_ms_per_step": e2e_wall_ms / args.steps, "h2d_ms": s2["h2d_ms"], "d2h_ms": s2["d2h_ms"]},
+                "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(p, values, residuals, D)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        g.close()
+        dist.destroy_process_group()
+
+
+def cpu_baseline(p, values, residuals, D):
+    """Oracle port of the reference's CPU path, all host threads, one full solve of the same problem."""
+    from oracle import binding as ob
+    st = p.structure
+    cores = os.cpu_count()
+    ost = ob.Structure(st.row_size, st.row_pos, st.cell_ptr, st.cell_block_id, st.cell_position, st.col_size,
+                       st.col_pos, st.num_eliminate_blocks)
+    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=MAX_PCG, native=True)
+    t0 = time.perf_counter()
+    _, s = o.solve(values, residuals, D, ETA, -1.0)
+    dt = time.perf_counter() - t0
+    return {"value": 1.0 / dt, "unit": "LM iters/s", "cores": cores, "kind": "port",
+            "sample": f"1 full solve of the same problem ({s['num_iterations']} PCG iterations, {dt:.2f} s)",
+            "pcg_iters_per_sec": s["num_iterations"] / dt}
+
+
+if __name__ == "__main__":
+    main()

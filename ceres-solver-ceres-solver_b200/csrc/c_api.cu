@@ -1,0 +1,295 @@
+// libceres_b200_schur.so — C ABI (include/ceres_b200_schur.h) over the CUDA
+// kernels. Host orchestration of IterativeSchurComplementSolver::SolveImpl
+// (iterative_schur_complement_solver.cc:64-157) with every vector, scalar and
+// convergence test resident on the device.
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+
+#include "camera_kernels.cuh"
+#include "cg_kernels.cuh"
+#include "kernels.cuh"
+#include "solver_state.h"
+
+using namespace cb200;
+
+namespace {
+
+thread_local std::string g_error;
+
+int Fail(int code, const std::string& msg) {
+  g_error = msg;
+  return code;
+}
+
+#define CUDA_OK(expr)                                                                  \
+  do {                                                                                 \
+    cudaError_t e_ = (expr);                                                           \
+    if (e_ != cudaSuccess)                                                             \
+      return Fail(CB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+#define CHECK_OK(expr)        \
+  do {                        \
+    int rc_ = (expr);         \
+    if (rc_ != CB200_OK) return rc_; \
+  } while (0)
+
+template <typename T>
+int DeviceAlloc(cb200_solver* s, T** ptr, size_t count) {
+  *ptr = nullptr;
+  if (count == 0) count = 1;
+  CUDA_OK(cudaMalloc(reinterpret_cast<void**>(ptr), count * sizeof(T)));
+  s->allocations.push_back(*ptr);
+  return CB200_OK;
+}
+
+template <typename T>
+int DeviceUpload(cb200_solver* s, T** ptr, const std::vector<T>& host) {
+  CHECK_OK(DeviceAlloc(s, ptr, host.size()));
+  if (!host.empty())
+    CUDA_OK(cudaMemcpy(*ptr, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return CB200_OK;
+}
+
+int LoadNccl(Nccl* n) {
+  if (n->lib != nullptr) return CB200_OK;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* name : names) {
+    n->lib = dlopen(name, RTLD_NOW | RTLD_GLOBAL);
+    if (n->lib) break;
+  }
+  if (!n->lib) return Fail(CB200_ERR_NCCL, std::string("dlopen libnccl: ") + dlerror());
+  n->GetUniqueId = reinterpret_cast<decltype(n->GetUniqueId)>(dlsym(n->lib, "ncclGetUniqueId"));
+  n->CommInitRank = reinterpret_cast<decltype(n->CommInitRank)>(dlsym(n->lib, "ncclCommInitRank"));
+  n->AllReduce = reinterpret_cast<decltype(n->AllReduce)>(dlsym(n->lib, "ncclAllReduce"));
+  n->CommDestroy = reinterpret_cast<decltype(n->CommDestroy)>(dlsym(n->lib, "ncclCommDestroy"));
+  n->GetErrorString = reinterpret_cast<decltype(n->GetErrorString)>(dlsym(n->lib, "ncclGetErrorString"));
+  if (!n->GetUniqueId || !n->CommInitRank || !n->AllReduce || !n->CommDestroy)
+    return Fail(CB200_ERR_NCCL, "libnccl lacks a required symbol");
+  return CB200_OK;
+}
+
+// Sum a device buffer over all ranks (camera-sized data only).
+int AllReduce(cb200_solver* s, double* buf, size_t count) {
+  if (s->opt.world_size <= 1) return CB200_OK;
+  const int rc = s->nccl.AllReduce(buf, buf, count, /*ncclDouble*/ 8, /*ncclSum*/ 0, s->nccl.comm, s->stream);
+  if (rc != 0)
+    return Fail(CB200_ERR_NCCL, std::string("ncclAllReduce: ") +
+                                    (s->nccl.GetErrorString ? s->nccl.GetErrorString(rc) : "error"));
+  return CB200_OK;
+}
+
+inline int Blocks(long long n, int threads) { return (int)((n + threads - 1) / threads); }
+
+}  // namespace
+
+extern "C" {
+
+const char* cb200_last_error(void) { return g_error.c_str(); }
+int cb200_version(void) { return 100; }
+
+int cb200_nccl_unique_id(char* out128) {
+  if (!out128) return Fail(CB200_ERR_INVALID_ARGUMENT, "null output");
+  Nccl n;
+  CHECK_OK(LoadNccl(&n));
+  UniqueId id;
+  const int rc = n.GetUniqueId(&id);
+  if (rc != 0) return Fail(CB200_ERR_NCCL, "ncclGetUniqueId failed");
+  std::memcpy(out128, id.internal, 128);
+  return CB200_OK;
+}
+
+void cb200_destroy(cb200_solver* s) {
+  if (!s) return;
+  if (s->opt.device_id >= 0) cudaSetDevice(s->opt.device_id);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
+  for (void* p : s->allocations) cudaFree(p);
+  if (s->h_cg) cudaFreeHost(s->h_cg);
+  for (auto& e : s->ev)
+    if (e) cudaEventDestroy(e);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+}
+
+int cb200_create(const cb200_structure* structure, const cb200_options* options, cb200_solver** out) {
+  if (!structure || !options || !out) return Fail(CB200_ERR_INVALID_ARGUMENT, "null argument");
+  *out = nullptr;
+  const cb200_options& o = *options;
+  if (o.preconditioner_type < CB200_IDENTITY || o.preconditioner_type > CB200_SCHUR_POWER_SERIES_EXPANSION)
+    return Fail(CB200_ERR_INVALID_ARGUMENT,
+                "unsupported preconditioner_type (CLUSTER_JACOBI / CLUSTER_TRIDIAGONAL are not "
+                "implemented on the device and there is no CPU fallback)");
+  if (o.world_size < 1 || o.rank < 0 || o.rank >= o.world_size)
+    return Fail(CB200_ERR_INVALID_ARGUMENT, "bad rank / world_size");
+  if (o.world_size > 1 && !o.nccl_unique_id)
+    return Fail(CB200_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
+  if (o.residual_reset_period <= 0 || o.max_num_iterations < 0 || o.min_num_iterations < 0)
+    return Fail(CB200_ERR_INVALID_ARGUMENT, "bad iteration options");
+
+  FlatStructure flat;
+  std::string err;
+  const int rc = Flatten(*structure, o.num_eliminate_blocks, &flat, &err);
+  if (rc != CB200_OK) return Fail(rc, err);
+  if (flat.num_obs == 0 || flat.num_cameras == 0 || flat.num_points == 0)
+    return Fail(CB200_ERR_UNSUPPORTED_STRUCTURE, "empty problem");
+
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    return Fail(CB200_ERR_CUDA, "no CUDA device (this library has no CPU fallback)");
+  if (o.device_id < 0 || o.device_id >= ndev) return Fail(CB200_ERR_INVALID_ARGUMENT, "bad device_id");
+  CUDA_OK(cudaSetDevice(o.device_id));
+
+  cb200_solver* s = new cb200_solver;
+  s->opt = o;
+  s->opt.nccl_unique_id = nullptr;
+  s->P = flat.num_points; s->C = flat.num_cameras; s->N = flat.num_obs;
+  s->canonical = flat.canonical_layout;
+  const std::vector<int> bounds = ShardPoints(flat.point_row_start, o.world_size);
+  s->p_begin = bounds[o.rank]; s->p_end = bounds[o.rank + 1];
+  s->r_begin = flat.point_row_start[s->p_begin]; s->r_end = flat.point_row_start[s->p_end];
+  s->P_loc = s->p_end - s->p_begin; s->N_loc = s->r_end - s->r_begin;
+  s->nvec = 9 * s->C;
+  s->vec_blocks = std::min(kMaxVecBlocks, Blocks(s->nvec, kVecThreads));
+  s->nrep = o.y_replicas > 0 ? o.y_replicas : 8;
+  s->rep_stride = (s->nvec + 31) / 32 * 32;
+
+  auto cleanup_fail = [&](int code) { cb200_destroy(s); return code; };
+#define TRY(expr) do { int rc2_ = (expr); if (rc2_ != CB200_OK) return cleanup_fail(rc2_); } while (0)
+#define TRY_CUDA(expr) do { cudaError_t e2_ = (expr); if (e2_ != cudaSuccess) { Fail(CB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e2_)); return cleanup_fail(CB200_ERR_CUDA); } } while (0)
+
+  TRY_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  for (auto& e : s->ev) TRY_CUDA(cudaEventCreate(&e));
+
+  // local structure arrays
+  std::vector<int> row_start(s->P_loc + 1), cam(s->N_loc);
+  for (int p = 0; p <= s->P_loc; ++p) row_start[p] = flat.point_row_start[s->p_begin + p] - s->r_begin;
+  std::copy(flat.cam_idx.begin() + s->r_begin, flat.cam_idx.begin() + s->r_end, cam.begin());
+  const TilePlan plan = PlanTiles(row_start.data(), s->P_loc);
+  s->num_tiles = (int)plan.tile_point.size() - 1;
+  s->num_long = (int)plan.long_points.size();
+
+  // camera-major order of the local rows, cut into chunks of one camera each
+  std::vector<int> cam_count(s->C + 1, 0);
+  for (int r = 0; r < s->N_loc; ++r) ++cam_count[cam[r] + 1];
+  std::partial_sum(cam_count.begin(), cam_count.end(), cam_count.begin());
+  std::vector<int> cam_perm(s->N_loc), cursor(cam_count.begin(), cam_count.end() - 1);
+  for (int r = 0; r < s->N_loc; ++r) cam_perm[cursor[cam[r]]++] = r;
+  std::vector<int> chunk_begin, cam_chunk_start(s->C + 1, 0);
+  for (int c = 0; c < s->C; ++c) {
+    cam_chunk_start[c] = (int)chunk_begin.size();
+    for (int b = cam_count[c]; b < cam_count[c + 1]; b += kChunkObs) chunk_begin.push_back(b);
+  }
+  cam_chunk_start[s->C] = (int)chunk_begin.size();
+  s->num_chunks = (int)chunk_begin.size();
+  chunk_begin.push_back(s->N_loc);
+  // a chunk must end where its camera ends: fix the per-chunk end by storing
+  // explicit begins only (end = next begin) -- true because chunks are emitted
+  // camera by camera in camera-major order.
+
+  // duplicate (point, camera) pairs
+  std::vector<int> dup_pairs;
+  {
+    std::vector<std::pair<int, int>> cr;
+    for (int p = 0; p < s->P_loc; ++p) {
+      cr.clear();
+      for (int r = row_start[p]; r < row_start[p + 1]; ++r) cr.emplace_back(cam[r], r);
+      std::sort(cr.begin(), cr.end());
+      for (size_t i = 0; i < cr.size(); ++i)
+        for (size_t j = i + 1; j < cr.size() && cr[j].first == cr[i].first; ++j) {
+          dup_pairs.push_back(p); dup_pairs.push_back(cr[i].second); dup_pairs.push_back(cr[j].second);
+        }
+    }
+  }
+  s->num_dup_pairs = (int)dup_pairs.size() / 3;
+
+  TRY(DeviceUpload(s, &s->d_cam, cam));
+  TRY(DeviceUpload(s, &s->d_row_start, row_start));
+  TRY(DeviceUpload(s, &s->d_tile_point, plan.tile_point));
+  TRY(DeviceUpload(s, &s->d_long_points, plan.long_points));
+  TRY(DeviceUpload(s, &s->d_cam_perm, cam_perm));
+  TRY(DeviceUpload(s, &s->d_chunk_begin, chunk_begin));
+  TRY(DeviceUpload(s, &s->d_cam_chunk_start, cam_chunk_start));
+  TRY(DeviceUpload(s, &s->d_dup_pairs, dup_pairs));
+  if (!s->canonical) {
+    std::vector<int> e_pos(flat.e_pos.begin() + s->r_begin, flat.e_pos.begin() + s->r_end);
+    std::vector<int> f_pos(flat.f_pos.begin() + s->r_begin, flat.f_pos.begin() + s->r_end);
+    TRY(DeviceUpload(s, &s->d_e_pos, e_pos));
+    TRY(DeviceUpload(s, &s->d_f_pos, f_pos));
+    long long max_pos = 0;
+    for (int r = 0; r < s->N; ++r)
+      max_pos = std::max<long long>(max_pos, std::max((long long)flat.e_pos[r] + 6, (long long)flat.f_pos[r] + 18));
+    s->staging_len = (size_t)max_pos;
+    TRY(DeviceAlloc(s, &s->d_values_staging, s->staging_len));
+  }
+  const size_t Nl = s->N_loc, Pl = s->P_loc, nv = s->nvec;
+  TRY(DeviceAlloc(s, &s->d_E, Nl * 6));
+  TRY(DeviceAlloc(s, &s->d_F, Nl * 18));
+  TRY(DeviceAlloc(s, &s->d_b, Nl * 2));
+  TRY(DeviceAlloc(s, &s->d_De, Pl * 3));
+  TRY(DeviceAlloc(s, &s->d_Df, nv));
+  TRY(DeviceAlloc(s, &s->d_ete_inv, Pl * 9));
+  TRY(DeviceAlloc(s, &s->d_weights, Nl * 3));
+  TRY(DeviceAlloc(s, &s->d_chunk_partial, (size_t)s->num_chunks * 45));
+  TRY(DeviceAlloc(s, &s->d_upper, (size_t)s->C * 45));
+  TRY(DeviceAlloc(s, &s->d_dup_blocks, (size_t)s->C * 81));
+  TRY(DeviceAlloc(s, &s->d_sj, (size_t)s->C * 81));
+  TRY(DeviceAlloc(s, &s->d_ftf_inv, (size_t)s->C * 81));
+  TRY(DeviceAlloc(s, &s->d_yrep, (size_t)s->nrep * s->rep_stride));
+  TRY(DeviceAlloc(s, &s->d_y_e, Pl * 3));
+  double** vecs[] = {&s->d_rhs, &s->d_x, &s->d_r, &s->d_p, &s->d_z, &s->d_q, &s->d_t1, &s->d_t2};
+  for (double** v : vecs) TRY(DeviceAlloc(s, v, nv));
+  TRY(DeviceAlloc(s, &s->d_rows, Nl * 2));
+  TRY(DeviceAlloc(s, &s->d_pts, Pl * 3));
+  TRY(DeviceAlloc(s, &s->d_cg, 1));
+  TRY_CUDA(cudaMemset(s->d_cg, 0, sizeof(CgState)));
+  TRY_CUDA(cudaMemset(s->d_yrep, 0, (size_t)s->nrep * s->rep_stride * sizeof(double)));
+  TRY_CUDA(cudaMemset(s->d_x, 0, nv * sizeof(double)));
+  TRY_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s->h_cg), sizeof(CgState)));
+  std::memset(s->h_cg, 0, sizeof(CgState));
+
+  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeSx>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
+  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModePseZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
+  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeRhs>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
+  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeBack>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
+
+  if (o.world_size > 1) {
+    TRY(LoadNccl(&s->nccl));
+    UniqueId id;
+    std::memcpy(id.internal, o.nccl_unique_id, 128);
+    const int nrc = s->nccl.CommInitRank(&s->nccl.comm, o.world_size, id, o.rank);
+    if (nrc != 0) {
+      Fail(CB200_ERR_NCCL, std::string("ncclCommInitRank: ") +
+                               (s->nccl.GetErrorString ? s->nccl.GetErrorString(nrc) : "error"));
+      return cleanup_fail(CB200_ERR_NCCL);
+    }
+  }
+#undef TRY
+#undef TRY_CUDA
+  *out = s;
+  return CB200_OK;
+}
+
+int cb200_num_rows(const cb200_solver* s) { return s ? 2 * s->N : 0; }
+int cb200_num_cols(const cb200_solver* s) { return s ? 3 * s->P + 9 * s->C : 0; }
+int cb200_num_cols_e(const cb200_solver* s) { return s ? 3 * s->P : 0; }
+int cb200_num_cols_f(const cb200_solver* s) { return s ? 9 * s->C : 0; }
+int cb200_shard(const cb200_solver* s, int* pb, int* pe, int* rb, int* re) {
+  if (!s) return Fail(CB200_ERR_INVALID_ARGUMENT, "null solver");
+  if (pb) *pb = s->p_begin;
+  if (pe) *pe = s->p_end;
+  if (rb) *rb = s->r_begin;
+  if (re) *re = s->r_end;
+  return CB200_OK;
+}
+
+}  // extern "C"
+
+#include "c_api_solve.inc"
+#include "c_api_entry.inc"

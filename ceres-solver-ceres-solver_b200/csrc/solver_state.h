@@ -1,0 +1,74 @@
+// Host-side state of one solver handle (one process, one GPU, one point shard).
+#ifndef CB200_SOLVER_STATE_H_
+#define CB200_SOLVER_STATE_H_
+
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "cg_kernels.cuh"
+#include "flatten.h"
+
+namespace cb200 {
+
+// Minimal NCCL binding resolved with dlopen at first use, so single-GPU
+// processes never load (or need) libnccl.
+struct UniqueId { char internal[128]; };  // ncclUniqueId (nccl.h: NCCL_UNIQUE_ID_BYTES 128)
+struct Nccl {
+  void* lib = nullptr;
+  void* comm = nullptr;
+  int (*GetUniqueId)(UniqueId*) = nullptr;
+  int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+
+}  // namespace cb200
+
+struct cb200_solver {
+  cb200_options opt{};
+  // global sizes
+  int P = 0, C = 0, N = 0;
+  bool canonical = false;
+  // shard
+  int p_begin = 0, p_end = 0, r_begin = 0, r_end = 0;
+  int P_loc = 0, N_loc = 0;
+  int nvec = 0;           // 9C
+  int vec_blocks = 0;     // CTAs of the camera-vector kernels
+  int num_tiles = 0, num_long = 0, num_chunks = 0, num_dup_pairs = 0;
+  int nrep = 0, rep_stride = 0;
+  bool has_D = false, values_resident = false, b_resident = false, isc_ready = false;
+  bool sj_ready = false;
+
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[8] = {};
+
+  // device: structure
+  int *d_cam = nullptr, *d_row_start = nullptr, *d_tile_point = nullptr, *d_long_points = nullptr;
+  int *d_cam_perm = nullptr, *d_chunk_begin = nullptr, *d_cam_chunk_start = nullptr, *d_dup_pairs = nullptr;
+  int *d_e_pos = nullptr, *d_f_pos = nullptr;
+  // device: values
+  double *d_E = nullptr, *d_F = nullptr, *d_b = nullptr, *d_De = nullptr, *d_Df = nullptr;
+  double *d_values_staging = nullptr;  // non-canonical layouts only
+  size_t staging_len = 0;
+  // device: derived
+  double *d_ete_inv = nullptr, *d_weights = nullptr, *d_chunk_partial = nullptr, *d_upper = nullptr;
+  double *d_dup_blocks = nullptr, *d_sj = nullptr, *d_ftf_inv = nullptr;
+  double *d_yrep = nullptr, *d_y_e = nullptr;
+  // device: camera vectors
+  double *d_rhs = nullptr, *d_x = nullptr, *d_r = nullptr, *d_p = nullptr, *d_z = nullptr, *d_q = nullptr;
+  double *d_t1 = nullptr, *d_t2 = nullptr, *d_rows = nullptr, *d_pts = nullptr;
+  cb200::CgState* d_cg = nullptr;
+  cb200::CgState* h_cg = nullptr;  // pinned; only the scalar head is copied back
+  double* d_trace = nullptr;
+  double* h_trace = nullptr;
+  int max_trace = 0;
+
+  cb200::Nccl nccl;
+  int launches = 0;
+  std::vector<void*> allocations;
+};
+
+#endif  // CB200_SOLVER_STATE_H_

@@ -1,0 +1,266 @@
+// Synthetic BAL (bundle adjustment in the large) problems of a named shape:
+// structure (which camera observes which point), scene geometry, and the
+// Snavely reprojection residuals / Jacobian blocks written directly in the
+// value layout Ceres' BlockJacobianWriter produces for an ITERATIVE_SCHUR
+// problem (all 2x3 point blocks "E" first in row order, then all 2x9 camera
+// blocks "F"; rows sorted by point; reference:
+// internal/ceres/block_jacobian_writer.cc:102-165, reorder_program.cc:446-540).
+//
+// Host-only measurement / test support (no CUDA, no oracle): the BAL data files
+// are not shipped with the reference and there is no network, so problems of the
+// BASELINE.json shapes are synthesised. Camera model follows
+// examples/snavely_reprojection_error.h:57-92 and the angle-axis rotation of
+// include/ceres/rotation.h:792-850; derivatives come from a small forward-mode
+// dual number type instead of ceres::Jet.
+//
+// Build: g++ -O3 -fopenmp -shared -fPIC synthetic_bal.cc -o libsynthetic_bal.so
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <numeric>
+#include <random>
+#include <vector>
+
+namespace {
+
+// Forward-mode dual number with 12 partials: 9 camera + 3 point parameters.
+struct Dual {
+  double v;
+  double d[12];
+};
+inline Dual Const(double c) { Dual r; r.v = c; std::memset(r.d, 0, sizeof(r.d)); return r; }
+inline Dual Var(double c, int k) { Dual r = Const(c); r.d[k] = 1.0; return r; }
+inline Dual operator+(const Dual& a, const Dual& b) {
+  Dual r; r.v = a.v + b.v; for (int i = 0; i < 12; ++i) r.d[i] = a.d[i] + b.d[i]; return r;
+}
+inline Dual operator-(const Dual& a, const Dual& b) {
+  Dual r; r.v = a.v - b.v; for (int i = 0; i < 12; ++i) r.d[i] = a.d[i] - b.d[i]; return r;
+}
+inline Dual operator-(const Dual& a) {
+  Dual r; r.v = -a.v; for (int i = 0; i < 12; ++i) r.d[i] = -a.d[i]; return r;
+}
+inline Dual operator*(const Dual& a, const Dual& b) {
+  Dual r; r.v = a.v * b.v;
+  for (int i = 0; i < 12; ++i) r.d[i] = a.d[i] * b.v + a.v * b.d[i];
+  return r;
+}
+inline Dual operator/(const Dual& a, const Dual& b) {
+  Dual r; const double inv = 1.0 / b.v; r.v = a.v * inv;
+  for (int i = 0; i < 12; ++i) r.d[i] = (a.d[i] - r.v * b.d[i]) * inv;
+  return r;
+}
+inline Dual Scale(const Dual& a, double f, double df) {  // chain rule helper
+  Dual r; r.v = f; for (int i = 0; i < 12; ++i) r.d[i] = df * a.d[i]; return r;
+}
+inline Dual Sqrt(const Dual& a) { const double s = std::sqrt(a.v); return Scale(a, s, 0.5 / s); }
+inline Dual Sin(const Dual& a) { return Scale(a, std::sin(a.v), std::cos(a.v)); }
+inline Dual Cos(const Dual& a) { return Scale(a, std::cos(a.v), -std::sin(a.v)); }
+
+template <typename T> inline T Lift(double c);
+template <> inline double Lift<double>(double c) { return c; }
+template <> inline Dual Lift<Dual>(double c) { return Const(c); }
+inline double Val(double a) { return a; }
+inline double Val(const Dual& a) { return a.v; }
+inline double Sqrt(double a) { return std::sqrt(a); }
+inline double Sin(double a) { return std::sin(a); }
+inline double Cos(double a) { return std::cos(a); }
+
+// Rodrigues rotation of pt by the angle-axis vector aa, with the first-order
+// branch near zero so derivatives stay finite (rotation.h:792-850).
+template <typename T>
+inline void RotateByAngleAxis(const T* aa, const T* pt, T* out) {
+  const T theta2 = aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2];
+  if (Val(theta2) > 2.220446049250313e-16) {
+    const T theta = Sqrt(theta2);
+    const T c = Cos(theta), s = Sin(theta);
+    const T inv = Lift<T>(1.0) / theta;
+    const T w[3] = {aa[0] * inv, aa[1] * inv, aa[2] * inv};
+    const T wxp[3] = {w[1] * pt[2] - w[2] * pt[1], w[2] * pt[0] - w[0] * pt[2],
+                      w[0] * pt[1] - w[1] * pt[0]};
+    const T k = (w[0] * pt[0] + w[1] * pt[1] + w[2] * pt[2]) * (Lift<T>(1.0) - c);
+    for (int i = 0; i < 3; ++i) out[i] = pt[i] * c + wxp[i] * s + w[i] * k;
+  } else {
+    out[0] = pt[0] + (aa[1] * pt[2] - aa[2] * pt[1]);
+    out[1] = pt[1] + (aa[2] * pt[0] - aa[0] * pt[2]);
+    out[2] = pt[2] + (aa[0] * pt[1] - aa[1] * pt[0]);
+  }
+}
+
+// Snavely / Bundler camera: 3 angle-axis, 3 translation, focal, k1, k2
+// (snavely_reprojection_error.h:57-92). Returns the predicted image position.
+template <typename T>
+inline void Project(const T* cam, const T* pt, T* pred) {
+  T p[3];
+  RotateByAngleAxis(cam, pt, p);
+  p[0] = p[0] + cam[3]; p[1] = p[1] + cam[4]; p[2] = p[2] + cam[5];
+  const T xp = -(p[0] / p[2]);
+  const T yp = -(p[1] / p[2]);
+  const T r2 = xp * xp + yp * yp;
+  const T distortion = Lift<T>(1.0) + r2 * (cam[7] + cam[8] * r2);
+  pred[0] = cam[6] * distortion * xp;
+  pred[1] = cam[6] * distortion * yp;
+}
+
+}  // namespace
+
+extern "C" {
+
+// Observation structure of a BAL-like problem with exactly C cameras, P points
+// and N observations. point_row_start[P+1] (rows are grouped by point), cam_idx[N]
+// ascending within a point. Track lengths are 2 + geometric, capped at C and
+// nudged to sum to N; cameras of a point cluster around a popularity-weighted
+// "home" camera (spatial locality + skewed per-camera counts, like real BAL).
+// dup_pairs > 0 forces that many points to observe one camera twice (exercises
+// the duplicate (point, camera) merge of schur_eliminator_impl.h:140-148).
+// Returns 0, or -1 when the shape is infeasible (N < 2P or N > P*C).
+int bal_synth_structure(int C, int P, long long N, unsigned long long seed,
+                        int dup_pairs, int* point_row_start, int* cam_idx) {
+  if (C < 1 || P < 1) return -1;
+  const int min_len = C >= 2 ? 2 : 1;
+  if (N < (long long)min_len * P || N > (long long)P * C) return -1;
+  std::mt19937_64 rng(seed);
+  std::vector<int> len(P);
+  const double mean_extra = (double)N / P - min_len;
+  std::geometric_distribution<int> geo(1.0 / (1.0 + std::max(mean_extra, 1e-9)));
+  long long sum = 0;
+  for (int p = 0; p < P; ++p) {
+    len[p] = std::min(C, min_len + (mean_extra > 0 ? geo(rng) : 0));
+    sum += len[p];
+  }
+  std::uniform_int_distribution<int> pick(0, P - 1);
+  while (sum != N) {
+    const int p = pick(rng);
+    if (sum < N && len[p] < C) { ++len[p]; ++sum; }
+    else if (sum > N && len[p] > min_len) { --len[p]; --sum; }
+  }
+  point_row_start[0] = 0;
+  for (int p = 0; p < P; ++p) {
+    const long long next = (long long)point_row_start[p] + len[p];
+    point_row_start[p + 1] = (int)next;
+  }
+  // camera popularity: log-normal weights -> cumulative table
+  std::normal_distribution<double> gauss(0.0, 1.0);
+  std::vector<double> cum(C);
+  double acc = 0.0;
+  for (int c = 0; c < C; ++c) { acc += std::exp(0.7 * gauss(rng)); cum[c] = acc; }
+  std::uniform_real_distribution<double> uni(0.0, 1.0);
+  const double spread = std::max(2.0, 0.02 * C);
+  std::vector<int> cams;
+  for (int p = 0; p < P; ++p) {
+    const int L = len[p];
+    cams.clear();
+    if (L * 2 > C) {  // dense track: sample without replacement
+      std::vector<int> all(C);
+      std::iota(all.begin(), all.end(), 0);
+      std::shuffle(all.begin(), all.end(), rng);
+      cams.assign(all.begin(), all.begin() + L);
+    } else {
+      const int home = (int)(std::lower_bound(cum.begin(), cum.end(), uni(rng) * acc) - cum.begin());
+      cams.push_back(std::min(home, C - 1));
+      double width = spread;
+      int tries = 0;
+      while ((int)cams.size() < L) {
+        // Laplace-distributed offset around the home camera, on a ring
+        const double u = uni(rng) - 0.5;
+        const int off = (int)std::lround(-width * (u < 0 ? -1 : 1) * std::log(1 - 2 * std::fabs(u)));
+        int c = ((cams[0] + off) % C + C) % C;
+        if (std::find(cams.begin(), cams.end(), c) == cams.end()) cams.push_back(c);
+        else if (++tries > 8) { width *= 2; tries = 0; }
+      }
+    }
+    std::sort(cams.begin(), cams.end());
+    std::copy(cams.begin(), cams.end(), cam_idx + point_row_start[p]);
+  }
+  // duplicates: the second observation of a point repeats the first's camera
+  for (int k = 0, p = 0; k < dup_pairs && p < P; ++p) {
+    if (len[p] >= 2) { cam_idx[point_row_start[p] + 1] = cam_idx[point_row_start[p]]; ++k; }
+  }
+  return 0;
+}
+
+// Scene at the scale BALProblem::Normalize() leaves (points with median absolute
+// deviation ~100, examples/bal_problem.cc:249-292): cameras on a ring of radius
+// 1000 looking at a point cloud around the origin; observations = projection of
+// the true scene + pixel noise; the returned parameters are then perturbed
+// (rotation / translation / point sigmas as in BALProblem::Perturb :294-333).
+void bal_synth_geometry(int C, int P, long long N, const int* point_row_start,
+                        const int* cam_idx, unsigned long long seed, double pixel_sigma,
+                        double rotation_sigma, double translation_sigma, double point_sigma,
+                        double* cameras, double* points, double* observations) {
+  std::mt19937_64 rng(seed ^ 0x9e3779b97f4a7c15ULL);
+  std::normal_distribution<double> gauss(0.0, 1.0);
+  std::uniform_real_distribution<double> uni(0.0, 1.0);
+  const double kPi = 3.14159265358979323846;
+  const double radius = 1000.0;
+  for (int c = 0; c < C; ++c) {
+    double* cam = cameras + 9 * c;
+    const double th = -kPi + 2.0 * kPi * (c + 0.5) / C;
+    // world position on the ring; R = rot_y(-th) maps it onto +z so the scene
+    // sits at negative camera z (Bundler convention)
+    const double cw[3] = {radius * std::sin(th), 20.0 * gauss(rng), radius * std::cos(th)};
+    double aa[3] = {0.02 * gauss(rng), -th + 0.02 * gauss(rng), 0.02 * gauss(rng)};
+    double rc[3];
+    RotateByAngleAxis<double>(aa, cw, rc);
+    cam[0] = aa[0]; cam[1] = aa[1]; cam[2] = aa[2];
+    cam[3] = -rc[0]; cam[4] = -rc[1]; cam[5] = -rc[2];
+    cam[6] = 500.0 + 1000.0 * uni(rng);
+    cam[7] = 1e-2 * gauss(rng);
+    cam[8] = 1e-3 * gauss(rng);
+  }
+  for (int p = 0; p < P; ++p)
+    for (int k = 0; k < 3; ++k) points[3 * p + k] = 120.0 * gauss(rng);
+  std::vector<int> row_point(N);
+  for (int p = 0; p < P; ++p)
+    for (int r = point_row_start[p]; r < point_row_start[p + 1]; ++r) row_point[r] = p;
+  for (long long r = 0; r < N; ++r) {
+    double pred[2];
+    Project<double>(cameras + 9 * cam_idx[r], points + 3 * row_point[r], pred);
+    observations[2 * r] = pred[0] + pixel_sigma * gauss(rng);
+    observations[2 * r + 1] = pred[1] + pixel_sigma * gauss(rng);
+  }
+  for (int c = 0; c < C; ++c) {
+    double* cam = cameras + 9 * c;
+    for (int k = 0; k < 3; ++k) cam[k] += rotation_sigma * gauss(rng);
+    for (int k = 3; k < 6; ++k) cam[k] += translation_sigma * gauss(rng);
+  }
+  for (long long i = 0; i < 3LL * P; ++i) points[i] += point_sigma * gauss(rng);
+}
+
+// Residuals [2N] and, when E/F are non-null, the Jacobian blocks E [N x 6]
+// (2x3 row-major, d residual / d point) and F [N x 18] (2x9 row-major,
+// d residual / d camera). Returns the cost 0.5 * |residuals|^2.
+double bal_evaluate(int P, long long N, const int* point_row_start, const int* cam_idx,
+                    const double* cameras, const double* points, const double* observations,
+                    double* residuals, double* E, double* F) {
+  double cost = 0.0;
+#pragma omp parallel for schedule(static) reduction(+ : cost)
+  for (int p = 0; p < P; ++p) {
+    for (int r = point_row_start[p]; r < point_row_start[p + 1]; ++r) {
+      const double* cam = cameras + 9 * cam_idx[r];
+      const double* pt = points + 3 * p;
+      double res[2];
+      if (E == nullptr) {
+        double pred[2];
+        Project<double>(cam, pt, pred);
+        res[0] = pred[0] - observations[2 * r];
+        res[1] = pred[1] - observations[2 * r + 1];
+      } else {
+        Dual dc[9], dp[3], pred[2];
+        for (int k = 0; k < 9; ++k) dc[k] = Var(cam[k], k);
+        for (int k = 0; k < 3; ++k) dp[k] = Var(pt[k], 9 + k);
+        Project<Dual>(dc, dp, pred);
+        for (int i = 0; i < 2; ++i) {
+          res[i] = pred[i].v - observations[2 * r + i];
+          for (int k = 0; k < 9; ++k) F[18LL * r + 9 * i + k] = pred[i].d[k];
+          for (int k = 0; k < 3; ++k) E[6LL * r + 3 * i + k] = pred[i].d[9 + k];
+        }
+      }
+      if (residuals) { residuals[2LL * r] = res[0]; residuals[2LL * r + 1] = res[1]; }
+      cost += 0.5 * (res[0] * res[0] + res[1] * res[1]);
+    }
+  }
+  return cost;
+}
+
+}  // extern "C"

@@ -1,0 +1,209 @@
+/* ceres_b200_schur.h — C ABI of libceres_b200_schur.so
+ *
+ * B200-native (sm_100a, FP64 CUDA) ITERATIVE_SCHUR linear solve for Ceres
+ * Solver's Levenberg-Marquardt loop. This header is the drop-in boundary: every
+ * entry point names the reference interface (file:line under the Ceres tree) it
+ * replaces. Plain pointers and sizes only; all pointers are HOST pointers unless
+ * a function says otherwise. INTEGRATION.md shows the C++ adapter
+ * (B200IterativeSchurComplementSolver : BlockSparseMatrixSolver) a Ceres
+ * maintainer adds on top of this header.
+ *
+ * There is no CPU fallback: every compute entry point fails with CB200_ERR_CUDA
+ * when no CUDA device is usable.
+ */
+#ifndef CERES_B200_SCHUR_H_
+#define CERES_B200_SCHUR_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes returned by every int function */
+enum {
+  CB200_OK = 0,
+  CB200_ERR_INVALID_ARGUMENT = -1,
+  CB200_ERR_UNSUPPORTED_STRUCTURE = -2, /* not a <2,3,9> Schur structure        */
+  CB200_ERR_CUDA = -3,
+  CB200_ERR_NCCL = -4,
+  CB200_ERR_STATE = -5                   /* call order (e.g. solve before upload) */
+};
+
+/* ceres::PreconditionerType values this solver accepts
+ * (include/ceres/types.h; iterative_schur_complement_solver.cc:159-199).
+ * CLUSTER_JACOBI / CLUSTER_TRIDIAGONAL are rejected at create time. */
+enum {
+  CB200_IDENTITY = 0,
+  CB200_JACOBI = 1,
+  CB200_SCHUR_JACOBI = 2,
+  CB200_SCHUR_POWER_SERIES_EXPANSION = 3
+};
+
+/* ceres::internal::LinearSolverTerminationType (linear_solver.h:57-74) */
+enum {
+  CB200_LINEAR_SOLVER_SUCCESS = 0,
+  CB200_LINEAR_SOLVER_NO_CONVERGENCE = 1,
+  CB200_LINEAR_SOLVER_FAILURE = 2,
+  CB200_LINEAR_SOLVER_FATAL_ERROR = 3
+};
+
+/* CompressedRowBlockStructure (block_structure.h:52-96) flattened into int
+ * arrays: row block r has size row_block_size[r], first scalar row
+ * row_block_pos[r], and cells cell_ptr[r] .. cell_ptr[r+1]-1, each with a column
+ * block id and the position of its row-major values in the values array. */
+typedef struct cb200_structure {
+  int num_row_blocks;
+  const int* row_block_size;
+  const int* row_block_pos;
+  const int* cell_ptr;       /* num_row_blocks + 1 */
+  const int* cell_block_id;
+  const int* cell_position;
+  int num_col_blocks;
+  const int* col_block_size;
+  const int* col_block_pos;
+} cb200_structure;
+
+/* Mirror of the LinearSolver::Options fields this solver consumes
+ * (linear_solver.h:150-230; iterative_schur_complement_solver.cc:74,100-129,178-186)
+ * plus the device placement. */
+typedef struct cb200_options {
+  int num_eliminate_blocks;   /* options.elimination_groups[0]                   */
+  int preconditioner_type;    /* CB200_* above                                   */
+  int min_num_iterations;     /* 0 in Solver::Options defaults (solver.h:594)    */
+  int max_num_iterations;
+  int residual_reset_period;  /* 10                                              */
+  int use_spse_initialization;
+  int max_num_spse_iterations;
+  double spse_tolerance;
+  /* device placement: one process per GPU. rank/world_size shard the points
+   * (and their residual rows) into contiguous ranges of balanced observation
+   * count; world_size > 1 needs nccl_unique_id (128 bytes from
+   * cb200_nccl_unique_id on rank 0, broadcast by the caller). */
+  int device_id;
+  int rank;
+  int world_size;
+  const char* nccl_unique_id;
+  int y_replicas;             /* 0 = default; privatised copies of the camera
+                                 accumulator that spread FP64 atomics           */
+  int status_check_period;    /* 0 = default; PCG iterations launched between
+                                 two reads of the device convergence flag       */
+} cb200_options;
+
+/* LinearSolver::Summary (linear_solver.h:320-326) + per-phase device timings. */
+typedef struct cb200_summary {
+  double residual_norm;       /* left at -1 like the reference                   */
+  int num_iterations;
+  int termination_type;
+  char message[512];
+  /* milliseconds, CUDA events on the solver's stream */
+  float h2d_ms, setup_ms, pcg_ms, back_substitute_ms, d2h_ms;
+  int kernel_launches;        /* kernels launched by the last solve              */
+} cb200_summary;
+
+typedef struct cb200_solver cb200_solver;
+
+const char* cb200_last_error(void);
+int cb200_version(void);
+
+/* 128-byte ncclUniqueId for a multi-process communicator (rank 0 calls it). */
+int cb200_nccl_unique_id(char* out128);
+
+/* LinearSolver::Create, case ITERATIVE_SCHUR (linear_solver.cc:111-116) +
+ * the first-call work of IterativeSchurComplementSolver::SolveImpl
+ * (iterative_schur_complement_solver.cc:76-83: DetectStructure,
+ * detect_structure.cc:39-120; PartitionedMatrixView ctor,
+ * partitioned_matrix_view_impl.h:47-105). Validates <2,3,9>, flattens the
+ * structure to device arrays, shards by point, allocates every device buffer. */
+int cb200_create(const cb200_structure* structure, const cb200_options* options,
+                 cb200_solver** out);
+void cb200_destroy(cb200_solver* s);
+
+/* sizes: num_cols = 3P + 9C (x), num_cols_f = 9C, num_rows = 2N. */
+int cb200_num_rows(const cb200_solver* s);
+int cb200_num_cols(const cb200_solver* s);
+int cb200_num_cols_e(const cb200_solver* s);
+int cb200_num_cols_f(const cb200_solver* s);
+/* this rank's point range [begin,end) and row-block range */
+int cb200_shard(const cb200_solver* s, int* point_begin, int* point_end,
+                int* row_block_begin, int* row_block_end);
+
+/* TypedLinearSolver<BlockSparseMatrix>::Solve -> SolveImpl
+ * (linear_solver.h:366-387; iterative_schur_complement_solver.cc:64-157).
+ * values = A->values() (full array, positions as in the structure), b has
+ * num_rows entries, D has num_cols entries or is NULL, x has num_cols entries;
+ * x is left untouched on FAILURE / FATAL_ERROR (:150-154). With world_size > 1
+ * each rank writes its own points' entries of x and all camera entries. */
+int cb200_solve(cb200_solver* s, const double* values, const double* b,
+                const double* D, double q_tolerance, double r_tolerance,
+                double* x, cb200_summary* summary);
+
+/* The same solve split at the host<->device copies (measurement with inputs
+ * resident in HBM; also what an on-device evaluator would call). Any of
+ * values / b / D may be NULL in cb200_upload to keep what is resident
+ * (D == NULL on the first upload means no regularisation). */
+int cb200_upload(cb200_solver* s, const double* values, const double* b,
+                 const double* D);
+int cb200_solve_resident(cb200_solver* s, double q_tolerance, double r_tolerance,
+                         cb200_summary* summary);
+int cb200_download_solution(cb200_solver* s, double* x);
+/* per_solve_options.D == nullptr for the following resident solves
+ * (linear_solver.h:237-257); the next cb200_upload with D != NULL re-enables it. */
+int cb200_clear_diagonal(cb200_solver* s);
+/* change min/max_num_iterations of an existing handle (fixed-work timing runs) */
+int cb200_set_iterations(cb200_solver* s, int min_num_iterations, int max_num_iterations);
+
+/* Iterate trace for parity tests: the reduced (camera) solution after each of
+ * the first max_trace PCG iterations of the next solves is kept on the device
+ * and copied into trace (max_trace x num_cols_f, row-major) at the end. */
+int cb200_set_trace(cb200_solver* s, double* trace, int max_trace);
+
+/* ---- finer-grained seams (unit parity, ncu); operate on uploaded values ---- */
+
+/* PartitionedMatrixView<2,3,9> products (partitioned_matrix_view_impl.h):
+ * RightMultiplyAndAccumulateE :112-137, RightMultiplyAndAccumulateF :139-191,
+ * LeftMultiplyAndAccumulateE :193-264, LeftMultiplyAndAccumulateF :266-375.
+ * y is read, accumulated into and written back (full-length host vectors;
+ * with world_size > 1 only this rank's rows / points contribute). */
+int cb200_pmv_right_e(cb200_solver* s, const double* x_e, double* y_rows);
+int cb200_pmv_right_f(cb200_solver* s, const double* x_f, double* y_rows);
+int cb200_pmv_left_e(cb200_solver* s, const double* x_rows, double* y_e);
+int cb200_pmv_left_f(cb200_solver* s, const double* x_rows, double* y_f);
+
+/* ImplicitSchurComplement::Init (implicit_schur_complement.cc:49-97):
+ * UpdateBlockDiagonalEtE (+FtF for JACOBI / SPSE), AddDiagonalAndInvert
+ * (:179-204), UpdateRhs (:251-276). */
+int cb200_isc_init(cb200_solver* s);
+int cb200_isc_ete_inverse(cb200_solver* s, double* out /* 9 * local points */);
+int cb200_isc_ftf_inverse(cb200_solver* s, double* out /* 81 * C */);
+int cb200_isc_rhs(cb200_solver* s, double* out /* 9C */);
+/* ImplicitSchurComplement::RightMultiplyAndAccumulate (:106-144): y = S x */
+int cb200_isc_multiply(cb200_solver* s, const double* x, double* y);
+/* InversePowerSeriesOperatorRightMultiplyAccumulate (:146-174): y += ... */
+int cb200_isc_pse_operator(cb200_solver* s, const double* x, double* y);
+/* BackSubstitute (:208-243): y = [ (E'E+D^2)^-1 E'(b - F z) ; z ] */
+int cb200_isc_back_substitute(cb200_solver* s, const double* z, double* y);
+
+/* SchurJacobiPreconditioner::UpdateImpl (schur_jacobi_preconditioner.cc:87-97):
+ * SchurEliminator<2,3,9>::Eliminate into a BlockRandomAccessDiagonalMatrix
+ * (schur_eliminator_impl.h:176-304) then Invert
+ * (block_random_access_diagonal_matrix.cc:90-100). invert == 0 stops before
+ * the inversion. blocks (81*C, row-major 9x9) may be NULL. D is the one last
+ * uploaded. */
+int cb200_schur_jacobi_update(cb200_solver* s, int invert, double* blocks);
+/* SchurJacobiPreconditioner::RightMultiplyAndAccumulate (:99-104): y += M^-1 x */
+int cb200_schur_jacobi_apply(cb200_solver* s, const double* x, double* y);
+/* PowerSeriesExpansionPreconditioner::RightMultiplyAndAccumulate
+ * (power_series_expansion_preconditioner.cc:57-82): y = sum Z^i (F'F)^-1 x */
+int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
+                    double spse_tolerance, const double* x, double* y);
+
+/* Device-resident timing of one op (CUDA events on the solver's stream, `iters`
+ * back-to-back launches after `warmup`); ms_out = average per launch.
+ * op: 0 S*x (isc multiply), 1 EtE inverse build, 2 rhs, 3 Schur-Jacobi build,
+ * 4 back substitute, 5 one PCG iteration (fixed work, no convergence test). */
+int cb200_time_op(cb200_solver* s, int op, int warmup, int iters, float* ms_out,
+                  int* launches_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CERES_B200_SCHUR_H_ */

@@ -1,0 +1,84 @@
+"""CPU tests of the product's host side: the C-ABI library loads and exports every symbol
+include/ceres_b200_schur.h declares, structure validation (DetectStructure rules,
+detect_structure.cc:39-120) rejects what is not <2,3,9> before touching the GPU, there is no
+CPU fallback, and the synthetic BAL generator produces the Jacobian of the Snavely model."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from tests import util
+from tests.golden import kat_problems as kp
+
+
+def test_library_exports_every_declared_symbol():
+    m = util.pkg()
+    L = m.solver.lib()
+    header = open(os.path.join(util.ROOT, "include", "ceres_b200_schur.h")).read()
+    declared = set(re.findall(r"\b(cb200_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    assert declared == set(m.solver.SYMBOLS), declared ^ set(m.solver.SYMBOLS)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.cb200_version() >= 100
+
+
+def test_unsupported_structures_are_rejected():
+    m = util.pkg()
+    # the reference's own KAT problems are scalar / mixed blocks: not <2,3,9>
+    for pid in (2, 4, 6):
+        st_kw, *_ = kp.flat(pid)
+        st = m.BlockStructure(**st_kw)
+        with pytest.raises(m.B200Error, match="cb200 error -2"):
+            m.IterativeSchurComplementSolver(st)
+    p = m.SyntheticBAL(5, 20, 60, geometry=False)
+    st = p.structure
+    with pytest.raises(m.B200Error, match="error -1"):
+        m.IterativeSchurComplementSolver(st, preconditioner_type=7)  # CLUSTER_* not supported
+    bad = m.BlockStructure.bal(p.point_row_start, p.cam_idx, 5)
+    bad.cell_block_id[0::2] = bad.cell_block_id[0::2][::-1].copy()  # rows not grouped by point
+    with pytest.raises(m.B200Error, match="error -2"):
+        m.IterativeSchurComplementSolver(bad)
+
+
+@pytest.mark.skipif(util.has_gpu(), reason="needs a machine without a GPU")
+def test_no_cpu_fallback():
+    m = util.pkg()
+    p = m.SyntheticBAL(5, 20, 60, geometry=False)
+    with pytest.raises(m.B200Error, match="error -3"):
+        m.IterativeSchurComplementSolver(p.structure)
+
+
+def test_synthetic_structure_shapes_and_determinism():
+    m = util.pkg()
+    p = m.SyntheticBAL(50, 2000, 9000, seed=1, dup_pairs=3)
+    q = m.SyntheticBAL(50, 2000, 9000, seed=1, dup_pairs=3)
+    assert np.array_equal(p.cam_idx, q.cam_idx) and np.array_equal(p.cameras, q.cameras)
+    lens = np.diff(p.point_row_start)
+    assert lens.sum() == 9000 and lens.min() >= 2 and p.cam_idx.max() < 50
+    dup = sum(len(set(p.cam_idx[a:b])) != b - a for a, b in zip(p.point_row_start[:-1], p.point_row_start[1:]))
+    assert dup == 3
+    with pytest.raises(ValueError):
+        m.SyntheticBAL(3, 10, 100)  # more observations than point-camera pairs
+
+
+def test_synthetic_jacobian_is_the_derivative():
+    m = util.pkg()
+    p = m.SyntheticBAL(6, 40, 150, seed=2)
+    cost, r0, values = p.evaluate()
+    assert abs(cost - 0.5 * r0 @ r0) < 1e-9 * cost
+    J = util.oracle_structure(p.structure).dense(values)
+    rng = np.random.default_rng(0)
+    d = rng.standard_normal(J.shape[1]) * 1e-6
+    dp, dc = d[:3 * p.P], d[3 * p.P:]
+    _, r1, _ = p.evaluate(cameras=p.cameras + dc, points=p.points + dp, jacobian=False)
+    _, r2, _ = p.evaluate(cameras=p.cameras - dc, points=p.points - dp, jacobian=False)
+    assert util.rel_err((r1 - r2) / 2, J @ d) < 1e-6
+    # column helpers agree with the dense matrix
+    assert util.rel_err(p.squared_column_norm(values), (J * J).sum(axis=0)) < 1e-13
+    x = rng.standard_normal(J.shape[1])
+    assert util.rel_err(p.jacobian_times(values, x), J @ x) < 1e-13
+    v2 = p.scale_columns(values.copy(), 1.0 / (1.0 + x * x))
+    assert util.rel_err(util.oracle_structure(p.structure).dense(v2), J / (1.0 + x * x)) < 1e-13

@@ -1,0 +1,226 @@
+"""GPU parity tests: every entry point of the C ABI (include/ceres_b200_schur.h) against the
+CPU oracle (oracle/, the restatement of the reference's ITERATIVE_SCHUR path) on the same
+seeded inputs. Tolerances (north_star): unit ops <= 1e-12 relative, PCG iterates and the
+solution <= 1e-9 relative, equal iteration counts and termination types.
+Modelled on implicit_schur_complement_test.cc, partitioned_matrix_view_test.cc,
+schur_eliminator_test.cc and iterative_schur_complement_solver_test.cc.
+"""
+import re
+
+import numpy as np
+import pytest
+
+from oracle import binding as ob
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+OP_TOL = 1e-12
+ITERATE_TOL = 1e-9
+
+
+def small_problem(C=7, P=60, N=260, seed=3, dup_pairs=0, interleaved=False):
+    m = util.pkg()
+    p = m.SyntheticBAL(C, P, N, seed=seed, dup_pairs=dup_pairs, geometry=False)
+    if interleaved:
+        p.structure = m.BlockStructure.bal(p.point_row_start, p.cam_idx, C, interleaved=True)
+    values, b, D = p.random_values(seed)
+    return m, p, values, b, D
+
+
+def to_interleaved(p, values):
+    N = p.N
+    out = np.empty_like(values)
+    v = out.reshape(N, 24)
+    v[:, :6] = values[:6 * N].reshape(N, 6)
+    v[:, 6:] = values[6 * N:].reshape(N, 18)
+    return out
+
+
+@pytest.mark.parametrize("dup_pairs,interleaved", [(0, False), (5, False), (0, True)])
+def test_unit_ops_match_oracle(dup_pairs, interleaved):
+    m, p, values, b, D = small_problem(dup_pairs=dup_pairs, interleaved=interleaved)
+    if interleaved:
+        values = to_interleaved(p, values)
+    st = p.structure
+    o = ob.Oracle(util.oracle_structure(st), preconditioner_type=ob.JACOBI)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=m.JACOBI)
+    g.upload(values, b, D)
+    rng = np.random.default_rng(1)
+    xe, xf, xr = (rng.standard_normal(n) for n in (st.num_cols_e, st.num_cols_f, st.num_rows))
+    # PartitionedMatrixView products
+    for op, x, n in [(0, xe, st.num_rows), (1, xf, st.num_rows), (2, xr, st.num_cols_e), (3, xr, st.num_cols_f)]:
+        y0 = rng.standard_normal(n)
+        want = o.pmv(values, op, x, y0.copy())
+        got = g.pmv(op, x, y0.copy())
+        assert util.rel_err(got, want) < OP_TOL, op
+    # ImplicitSchurComplement
+    o.isc_init(values, D, b)
+    g.isc_init()
+    assert util.rel_err(g.ete_inverse(), o.ete_inverse()) < OP_TOL
+    assert util.rel_err(g.ftf_inverse(), o.ftf_inverse()) < OP_TOL
+    assert util.rel_err(g.isc_rhs(), o.isc_rhs()) < OP_TOL
+    assert util.rel_err(g.isc_multiply(xf), o.isc_multiply(xf)) < OP_TOL
+    y0 = rng.standard_normal(st.num_cols_f)
+    assert util.rel_err(g.isc_pse_operator(xf, y0.copy()), o.isc_pse_operator(xf, y0.copy())) < OP_TOL
+    assert util.rel_err(g.isc_back_substitute(xf), o.isc_back_substitute(xf)) < OP_TOL
+    assert util.rel_err(g.pse_apply(xf, 5, 0.0), o.pse_apply(xf, 5, 0.0)) < OP_TOL
+    assert util.rel_err(g.pse_apply(xf, 50, 1e-3), o.pse_apply(xf, 50, 1e-3)) < 1e-10
+    # SchurJacobiPreconditioner
+    assert util.rel_err(g.schur_jacobi(invert=False), o.schur_jacobi(values, D, invert=False)) < OP_TOL
+    assert util.rel_err(g.schur_jacobi(invert=True), o.schur_jacobi(values, D, invert=True)) < 1e-11
+    Minv = g.schur_jacobi(invert=True).reshape(-1, 9, 9)
+    want = y0 + np.einsum("cij,cj->ci", Minv, xf.reshape(-1, 9)).reshape(-1)
+    assert util.rel_err(g.schur_jacobi_apply(xf, y0.copy()), want) < OP_TOL
+
+
+def test_schur_complement_is_the_dense_one():
+    """S e_i == column i of the dense Schur complement (implicit_schur_complement_test.cc:155-213)."""
+    m, p, values, b, D = small_problem(C=4, P=30, N=100)
+    st = p.structure
+    A = util.oracle_structure(st).dense(values)
+    H = A.T @ A + np.diag(D * D)
+    ne = st.num_cols_e
+    S = H[ne:, ne:] - H[ne:, :ne] @ np.linalg.solve(H[:ne, :ne], H[:ne, ne:])
+    g = m.IterativeSchurComplementSolver(st)
+    g.upload(values, b, D)
+    g.isc_init()
+    cols = np.stack([g.isc_multiply(e) for e in np.eye(st.num_cols_f)], axis=1)
+    assert np.abs(cols - S).max() < 1e-10 * np.abs(S).max()
+    g_rhs = A.T @ b
+    want = g_rhs[ne:] - H[ne:, :ne] @ np.linalg.solve(H[:ne, :ne], g_rhs[:ne])
+    assert util.rel_err(g.isc_rhs(), want) < 1e-11
+    sol = np.linalg.solve(H, g_rhs)
+    assert util.rel_err(g.isc_back_substitute(sol[ne:]), sol) < 1e-10
+
+
+PRECONDITIONERS = ["IDENTITY", "JACOBI", "SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION"]
+
+
+def compare_solve(m, st, values, b, D, ptype, q_tol=0.0, r_tol=1e-10, max_it=200, min_it=0,
+                  spse_init=False, threads=4, check_period=0, **kw):
+    code = PRECONDITIONERS.index(ptype)
+    o = ob.Oracle(util.oracle_structure(st), num_threads=threads, preconditioner_type=code,
+                  min_num_iterations=min_it, max_num_iterations=max_it,
+                  use_spse_initialization=spse_init)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, min_num_iterations=min_it,
+                                         max_num_iterations=max_it, use_spse_initialization=spse_init,
+                                         status_check_period=check_period, **kw)
+    ntrace = min(max_it, 64)
+    g.set_trace(ntrace)
+    xo, so = o.solve(values, b, D, q_tol, r_tol, max_trace=ntrace)
+    xg, sg = g.solve(values, b, D, q_tol, r_tol)
+    assert sg["termination_type"] == so["termination_type"], (sg, so)
+    assert sg["num_iterations"] == so["num_iterations"], (sg["message"], so["message"])
+    for k in range(len(so["trace"])):
+        assert util.rel_err(sg["trace"][k], so["trace"][k]) < ITERATE_TOL, k
+    assert util.rel_err(xg, xo) < ITERATE_TOL
+    strip = lambda t: re.sub(r"-?\d\.\d+e[-+]\d+", "#", t)  # same text, numbers may differ in the last digit
+    assert strip(sg["message"]) == strip(so["message"])
+    return xg, sg, so
+
+
+@pytest.mark.parametrize("ptype", PRECONDITIONERS)
+@pytest.mark.parametrize("use_D", [True, False])
+def test_solve_matches_oracle_small(ptype, use_D):
+    m, p, values, b, D = small_problem(C=9, P=200, N=900, seed=11)
+    x, sg, so = compare_solve(m, p.structure, values, b, D if use_D else None, ptype)
+    assert sg["termination_type"] == 0
+    # and the normal equations are solved (iterative_schur_complement_solver_test.cc:76-115)
+    A = util.oracle_structure(p.structure).dense(values)
+    H = A.T @ A + (np.diag(D * D) if use_D else 0)
+    assert util.rel_err(x, np.linalg.solve(H, A.T @ b)) < 1e-7
+
+
+@pytest.mark.parametrize("period", [1, 3, 7])
+def test_solve_q_tolerance_and_check_period(period):
+    """LM passes q_tolerance = eta, r_tolerance = -1 (levenberg_marquardt_strategy.cc:97-104);
+    iterations launched ahead of the device's convergence flag must not change the result."""
+    m, p, values, b, D = small_problem(C=9, P=200, N=900, seed=5)
+    compare_solve(m, p.structure, values, b, D, "SCHUR_JACOBI", q_tol=1e-2, r_tol=-1.0, check_period=period)
+
+
+def test_solve_min_max_iterations_and_spse_init():
+    m, p, values, b, D = small_problem(C=9, P=200, N=900, seed=6)
+    _, sg, _ = compare_solve(m, p.structure, values, b, D, "SCHUR_JACOBI", q_tol=-1.0, r_tol=-1.0,
+                             min_it=25, max_it=25)
+    assert sg["num_iterations"] == 25 and sg["termination_type"] == 1
+    compare_solve(m, p.structure, values, b, D, "SCHUR_POWER_SERIES_EXPANSION", spse_init=True)
+    compare_solve(m, p.structure, values, b, D, "SCHUR_JACOBI", max_it=0)
+
+
+def test_zero_rhs():
+    m, p, values, b, D = small_problem()
+    x, sg, so = compare_solve(m, p.structure, values, np.zeros_like(b), D, "SCHUR_JACOBI")
+    assert sg["num_iterations"] == 0 and sg["message"] == "Convergence. |b| = 0."
+    assert np.all(x == 0)
+
+
+def test_duplicate_and_long_points():
+    m = util.pkg()
+    # duplicates of a (point, camera) pair: schur_eliminator_impl.h:140-148
+    _, p, values, b, D = small_problem(C=9, P=200, N=900, seed=8, dup_pairs=40)
+    compare_solve(m, p.structure, values, b, D, "SCHUR_JACOBI")
+    # a point seen by 300 cameras does not fit one CTA tile
+    C, P = 300, 40
+    lens = np.full(P, 3)
+    lens[7] = 300
+    lens[20] = 257
+    prs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    rng = np.random.default_rng(0)
+    cam = np.concatenate([np.sort(rng.choice(C, size=L, replace=False)) for L in lens]).astype(np.int32)
+    st = m.BlockStructure.bal(prs, cam, C)
+    N = len(cam)
+    values, b, D = rng.standard_normal(24 * N), rng.standard_normal(2 * N), rng.standard_normal(3 * P + 9 * C) + 3
+    compare_solve(m, st, values, b, D, "SCHUR_JACOBI", r_tol=1e-8)
+    compare_solve(m, st, values, b, D, "SCHUR_POWER_SERIES_EXPANSION", r_tol=1e-6, max_it=30)
+
+
+@pytest.mark.parametrize("ptype", ["SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION"])
+def test_lm_shaped_solve_ladybug_scale(ptype):
+    """Snavely Jacobian, Jacobi scaling, D from the LM strategy, eta = 1e-2 (bundle_adjuster.cc:114)."""
+    m = util.pkg()
+    p = m.SyntheticBAL.named("ladybug", scale=0.1)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    compare_solve(m, p.structure, values, residuals, D, ptype, q_tol=1e-2, r_tol=-1.0, max_it=500, threads=8)
+
+
+def test_lm_shaped_solve_ladybug_full():
+    m = util.pkg()
+    p = m.SyntheticBAL.named("ladybug")
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    compare_solve(m, p.structure, values, residuals, D, "SCHUR_JACOBI", q_tol=1e-2, r_tol=-1.0, max_it=500,
+                  threads=8)
+
+
+def test_venice_full_size_properties():
+    """BASELINE.json's metric shape: too large for iterate-by-iterate oracle runs in a test, so
+    size-independent identities: S symmetric positive definite (x'Sy == y'Sx), S x equals the chain
+    of separate E/F products, and the solve drives the reduced residual down."""
+    m = util.pkg()
+    p = m.SyntheticBAL.named("venice", geometry=False)
+    values, b, D = p.random_values(1)
+    D = np.abs(D) + 1.0
+    st = p.structure
+    g = m.IterativeSchurComplementSolver(st, max_num_iterations=60)
+    g.upload(values, b, D)
+    g.isc_init()
+    rng = np.random.default_rng(2)
+    x, y = rng.standard_normal(st.num_cols_f), rng.standard_normal(st.num_cols_f)
+    Sx, Sy = g.isc_multiply(x), g.isc_multiply(y)
+    assert abs(y @ Sx - x @ Sy) < 1e-10 * abs(y @ Sx)
+    assert x @ Sx > 0
+    # chain: F x -> E' -> (E'E)^-1 -> E -> F'
+    rows = g.pmv(1, x, np.zeros(st.num_rows))
+    te = g.pmv(2, rows, np.zeros(st.num_cols_e))
+    inv = g.ete_inverse().reshape(-1, 3, 3)
+    te2 = -np.einsum("pij,pj->pi", inv, te.reshape(-1, 3)).reshape(-1)
+    rows = g.pmv(0, te2, rows)
+    want = g.pmv(3, rows, D[st.num_cols_e:] ** 2 * x)
+    assert util.rel_err(Sx, want) < 1e-11
+    # solve
+    s = g.solve_resident(0.0, 1e-8)
+    z = g.download_solution()
+    r = g.isc_rhs() - g.isc_multiply(z[st.num_cols_e:])
+    assert s["termination_type"] == 0, s
+    assert np.linalg.norm(r) <= 1.01e-8 * np.linalg.norm(g.isc_rhs())
