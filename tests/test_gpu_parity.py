@@ -97,8 +97,10 @@ def test_schur_complement_is_the_dense_one():
 PRECONDITIONERS = ["IDENTITY", "JACOBI", "SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION"]
 
 
-def compare_solve(m, st, values, b, D, ptype, q_tol=0.0, r_tol=1e-10, max_it=200, min_it=0,
+def compare_solve(m, st, values, b, D, ptype, q_tol=-1.0, r_tol=1e-10, max_it=200, min_it=0,
                   spse_init=False, threads=4, check_period=0, **kw):
+    # q_tol = -1 disables the Q test: with q_tol = 0 it fires on the SIGN of a round-off sized
+    # zeta (Q1 - Q0 ~ 1e-15 Q1 at convergence), which no two summation orders agree on.
     code = PRECONDITIONERS.index(ptype)
     o = ob.Oracle(util.oracle_structure(st), num_threads=threads, preconditioner_type=code,
                   min_num_iterations=min_it, max_num_iterations=max_it,
@@ -112,7 +114,7 @@ def compare_solve(m, st, values, b, D, ptype, q_tol=0.0, r_tol=1e-10, max_it=200
     xg, sg = g.solve(values, b, D, q_tol, r_tol)
     assert sg["termination_type"] == so["termination_type"], (sg, so)
     assert sg["num_iterations"] == so["num_iterations"], (sg["message"], so["message"])
-    for k in range(len(so["trace"])):
+    for k in range(len(so.get("trace", []))):
         assert util.rel_err(sg["trace"][k], so["trace"][k]) < ITERATE_TOL, k
     assert util.rel_err(xg, xo) < ITERATE_TOL
     strip = lambda t: re.sub(r"-?\d\.\d+e[-+]\d+", "#", t)  # same text, numbers may differ in the last digit
@@ -219,7 +221,7 @@ def test_venice_full_size_properties():
     want = g.pmv(3, rows, D[st.num_cols_e:] ** 2 * x)
     assert util.rel_err(Sx, want) < 1e-11
     # solve
-    s = g.solve_resident(0.0, 1e-8)
+    s = g.solve_resident(-1.0, 1e-8)
     z = g.download_solution()
     r = g.isc_rhs() - g.isc_multiply(z[st.num_cols_e:])
     assert s["termination_type"] == 0, s

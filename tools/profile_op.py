@@ -1,0 +1,43 @@
+#!/usr/bin/env python
+"""Run one device op of the solver back to back on a synthetic BAL shape (for ncu / quick timing).
+
+    python tools/profile_op.py --shape venice --op 6 --iters 5
+ops: see cb200_time_op in include/ceres_b200_schur.h
+"""
+import argparse
+import importlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shape", default="venice")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--op", type=int, nargs="+", default=[6])
+    ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--precond", type=int, default=2)
+    args = ap.parse_args()
+    pkg = importlib.import_module("ceres-solver-ceres-solver_b200")
+    p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, geometry=False)
+    values, b, D = p.random_values(1)
+    D = np.abs(D) + 1.0
+    g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=args.precond, max_num_iterations=50)
+    g.upload(values, b, D)
+    g.isc_init()
+    N, P, C = p.N, p.P, p.C
+    bytes_sx = 192 * N + 4 * N + 4 * P + 72 * P + 144 * C
+    for op in args.op:
+        ms, launches = g.time_op(op, warmup=args.warmup, iters=args.iters)
+        print(f"op {op}: {ms:.4f} ms/launch-group ({launches} launches); "
+              f"vs B_Sx={bytes_sx/1e9:.3f} GB -> {bytes_sx/ms/1e6:.0f} GB/s")
+
+
+if __name__ == "__main__":
+    main()
