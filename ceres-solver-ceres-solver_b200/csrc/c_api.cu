@@ -15,6 +15,7 @@
 #include "cg_kernels.cuh"
 #include "kernels.cuh"
 #include "solver_state.h"
+#include "stream_kernels.cuh"
 
 using namespace cb200;
 
@@ -171,9 +172,11 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   std::vector<int> row_start(s->P_loc + 1), cam(s->N_loc);
   for (int p = 0; p <= s->P_loc; ++p) row_start[p] = flat.point_row_start[s->p_begin + p] - s->r_begin;
   std::copy(flat.cam_idx.begin() + s->r_begin, flat.cam_idx.begin() + s->r_end, cam.begin());
-  const TilePlan plan = PlanTiles(row_start.data(), s->P_loc);
-  s->num_tiles = (int)plan.tile_point.size() - 1;
+  const TilePlan plan = PlanTiles(row_start.data(), cam.data(), s->P_loc);
+  s->num_tiles = (int)plan.tiles.size();
   s->num_long = (int)plan.long_points.size();
+  s->num_empty = (int)plan.empty_points.size();
+  TRY_CUDA(cudaDeviceGetAttribute(&s->num_sms, cudaDevAttrMultiProcessorCount, o.device_id));
 
   // camera-major order of the local rows, cut into chunks of one camera each
   std::vector<int> cam_count(s->C + 1, 0);
@@ -211,8 +214,9 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
 
   TRY(DeviceUpload(s, &s->d_cam, cam));
   TRY(DeviceUpload(s, &s->d_row_start, row_start));
-  TRY(DeviceUpload(s, &s->d_tile_point, plan.tile_point));
+  TRY(DeviceUpload(s, &s->d_tiles, plan.tiles));
   TRY(DeviceUpload(s, &s->d_long_points, plan.long_points));
+  TRY(DeviceUpload(s, &s->d_empty_points, plan.empty_points));
   TRY(DeviceUpload(s, &s->d_cam_perm, cam_perm));
   TRY(DeviceUpload(s, &s->d_chunk_begin, chunk_begin));
   TRY(DeviceUpload(s, &s->d_cam_chunk_start, cam_chunk_start));
@@ -234,7 +238,8 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   TRY(DeviceAlloc(s, &s->d_b, Nl * 2));
   TRY(DeviceAlloc(s, &s->d_De, Pl * 3));
   TRY(DeviceAlloc(s, &s->d_Df, nv));
-  TRY(DeviceAlloc(s, &s->d_ete_inv, Pl * 9));
+  TRY(DeviceAlloc(s, &s->d_ete_inv, Pl * 6));
+  TRY(DeviceAlloc(s, &s->d_ete9, Pl * 9));
   TRY(DeviceAlloc(s, &s->d_weights, Nl * 3));
   TRY(DeviceAlloc(s, &s->d_chunk_partial, (size_t)s->num_chunks * 45));
   TRY(DeviceAlloc(s, &s->d_upper, (size_t)s->C * 45));
@@ -254,10 +259,13 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   TRY_CUDA(cudaMallocHost(reinterpret_cast<void**>(&s->h_cg), sizeof(CgState)));
   std::memset(s->h_cg, 0, sizeof(CgState));
 
-  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeSx>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
-  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModePseZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
-  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeRhs>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
-  TRY_CUDA(cudaFuncSetAttribute(point_tile_kernel<kModeBack>, cudaFuncAttributeMaxDynamicSharedMemorySize, kPointSmemBytes));
+#define SET_SMEM(MODE, BUILD)                                                              \
+  TRY_CUDA(cudaFuncSetAttribute(point_stream_kernel<MODE, BUILD>,                          \
+                                cudaFuncAttributeMaxDynamicSharedMemorySize,               \
+                                StreamLayout<MODE, BUILD>::kSmemBytes))
+  SET_SMEM(kModeSx, false); SET_SMEM(kModePseZ, false); SET_SMEM(kModeRhs, false);
+  SET_SMEM(kModeBack, false); SET_SMEM(kModeRhs, true);
+#undef SET_SMEM
 
   if (o.world_size > 1) {
     TRY(LoadNccl(&s->nccl));

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -20,7 +21,7 @@
 
 namespace cb200 {
 
-constexpr int kTileObs = 256;  // observations per CTA tile of the fused kernels
+constexpr int kTileObs = 32;  // rows per tile of the fused per-point kernels: one lane each
 
 struct FlatStructure {
   int num_points = 0;      // P: eliminated (E) column blocks, size 3
@@ -115,34 +116,65 @@ inline std::vector<int> ShardPoints(const std::vector<int>& point_row_start, int
   return bounds;
 }
 
-// Tile plan of the fused per-point kernels: tile t covers whole points
-// [tile_point[t], tile_point[t+1]) whose rows fit kTileObs. Points with more
-// rows than a tile go to long_points (handled by a CTA-per-point kernel).
-// Indices are LOCAL to the shard (point 0 = first point of the shard).
+// Tile plan of the fused per-point kernels: a tile is the unit of work of ONE
+// WARP: whole points [p0, p0 + np) whose rows [r0, r0 + n) fit the 32 lanes.
+// Points with more rows than a tile go to long_points (CTA-per-point kernel),
+// points without rows to empty_points. Indices are LOCAL to the shard (point 0
+// = first point of the shard). One TileMeta record per tile is the static
+// side-band the device streams next to the Jacobian blocks (one bulk copy).
+struct alignas(16) TileMeta {
+  int r0, n, p0, np;
+  int cam[kTileObs];   // camera of each row
+  int seg[kTileObs];   // tile-local point | first lane of the point << 8 | last lane << 16
+};
+static_assert(sizeof(TileMeta) % 16 == 0, "bulk copies move multiples of 16 bytes");
+
 struct TilePlan {
-  std::vector<int> tile_point;   // T+1
-  std::vector<int> long_points;  // local point ids
+  std::vector<TileMeta> tiles;
+  std::vector<int> long_points;   // local point ids
+  std::vector<int> empty_points;  // local point ids
 };
 
-inline TilePlan PlanTiles(const int* row_start /* local, P_loc+1 */, int P_loc) {
+inline TilePlan PlanTiles(const int* row_start /* local, P_loc+1 */, const int* cam /* local rows */,
+                          int P_loc) {
   TilePlan plan;
-  plan.tile_point.push_back(0);
-  int tile_first = 0;
+  std::vector<int> members;  // non-empty points of the open tile
+  int open_rows = 0;
+  auto emit = [&]() {
+    if (members.empty()) return;
+    TileMeta m;
+    std::memset(&m, 0, sizeof(m));
+    const int p0 = members.front(), p1 = members.back() + 1;
+    m.r0 = row_start[p0];
+    m.n = row_start[p1] - m.r0;
+    m.p0 = p0;
+    m.np = p1 - p0;
+    for (int l = 0; l < kTileObs; ++l) m.seg[l] = 0 | (l << 8) | (l << 16);  // idle lanes: own segment
+    for (int p : members) {
+      const int first = row_start[p] - m.r0, last = row_start[p + 1] - 1 - m.r0;
+      for (int l = first; l <= last; ++l) {
+        m.cam[l] = cam[m.r0 + l];
+        m.seg[l] = (p - p0) | (first << 8) | (last << 16);
+      }
+    }
+    plan.tiles.push_back(m);
+    members.clear();
+    open_rows = 0;
+  };
   for (int p = 0; p < P_loc; ++p) {
     const int len = row_start[p + 1] - row_start[p];
+    if (len == 0) { plan.empty_points.push_back(p); continue; }  // (rows stay contiguous)
     if (len > kTileObs) {
-      if (p > tile_first) plan.tile_point.push_back(p);  // close the open tile
+      emit();
       plan.long_points.push_back(p);
-      plan.tile_point.push_back(p + 1);                  // empty-for-the-tile-kernel slot
-      tile_first = p + 1;
       continue;
     }
-    if (row_start[p + 1] - row_start[tile_first] > kTileObs || p - tile_first >= kTileObs) {
-      plan.tile_point.push_back(p);
-      tile_first = p;
-    }
+    if (open_rows + len > kTileObs) emit();
+    if (!members.empty() && p - members.front() >= kTileObs) emit();  // np <= kTileObs (empty points between)
+    members.push_back(p);
+    open_rows += len;
   }
-  if (plan.tile_point.back() != P_loc) plan.tile_point.push_back(P_loc);
+  emit();
   return plan;
 }
 

@@ -37,8 +37,9 @@ struct cb200_solver {
   int P_loc = 0, N_loc = 0;
   int nvec = 0;           // 9C
   int vec_blocks = 0;     // CTAs of the camera-vector kernels
-  int num_tiles = 0, num_long = 0, num_chunks = 0, num_dup_pairs = 0;
+  int num_tiles = 0, num_long = 0, num_empty = 0, num_chunks = 0, num_dup_pairs = 0;
   int nrep = 0, rep_stride = 0;
+  int num_sms = 0;        // persistent grids are sized in multiples of it
   bool has_D = false, values_resident = false, b_resident = false, isc_ready = false;
   bool sj_ready = false;
 
@@ -46,7 +47,8 @@ struct cb200_solver {
   cudaEvent_t ev[8] = {};
 
   // device: structure
-  int *d_cam = nullptr, *d_row_start = nullptr, *d_tile_point = nullptr, *d_long_points = nullptr;
+  int *d_cam = nullptr, *d_row_start = nullptr, *d_long_points = nullptr, *d_empty_points = nullptr;
+  cb200::TileMeta* d_tiles = nullptr;
   int *d_cam_perm = nullptr, *d_chunk_begin = nullptr, *d_cam_chunk_start = nullptr, *d_dup_pairs = nullptr;
   int *d_e_pos = nullptr, *d_f_pos = nullptr;
   // device: values
@@ -56,7 +58,7 @@ struct cb200_solver {
   // device: derived
   double *d_ete_inv = nullptr, *d_weights = nullptr, *d_chunk_partial = nullptr, *d_upper = nullptr;
   double *d_dup_blocks = nullptr, *d_sj = nullptr, *d_ftf_inv = nullptr;
-  double *d_yrep = nullptr, *d_y_e = nullptr;
+  double *d_yrep = nullptr, *d_y_e = nullptr, *d_ete9 = nullptr;
   // device: camera vectors
   double *d_rhs = nullptr, *d_x = nullptr, *d_r = nullptr, *d_p = nullptr, *d_z = nullptr, *d_q = nullptr;
   double *d_t1 = nullptr, *d_t2 = nullptr, *d_rows = nullptr, *d_pts = nullptr;

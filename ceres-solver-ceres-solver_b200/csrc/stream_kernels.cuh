@@ -1,0 +1,422 @@
+// The hot kernels: one persistent, TMA-pipelined pass over the Jacobian of a
+// point shard that performs a whole ImplicitSchurComplement product.
+//
+// Reference (what one launch replaces):
+//   ImplicitSchurComplement::RightMultiplyAndAccumulate  implicit_schur_complement.cc:106-144
+//     = RightMultiplyAndAccumulateF, LeftMultiplyAndAccumulateE, block-diagonal
+//       (E'E)^-1 multiply, RightMultiplyAndAccumulateE, LeftMultiplyAndAccumulateF
+//       (partitioned_matrix_view_impl.h:112-375, block_sparse_matrix.cc:239-274)
+//       and the ParallelSetZero / ParallelAssign passes over the 2N / 3P temporaries
+//   ImplicitSchurComplement::UpdateRhs                   :251-276
+//   ...::InversePowerSeriesOperatorRightMultiplyAccumulate :146-174
+//   ImplicitSchurComplement::BackSubstitute              :208-243
+//   (BUILD) UpdateBlockDiagonalEtE + AddDiagonalAndInvert
+//           partitioned_matrix_view_impl.h:446-523, implicit_schur_complement.cc:179-204
+//
+// Structure: persistent CTAs of kStreamWarps autonomous warps. A warp owns a
+// contiguous range of tiles (whole points, <= 32 rows: one lane per row) and a
+// private ring of shared-memory stages. Its elected lane streams the tile's E
+// rows, F rows, static side-band (TileMeta), (E'E)^-1 blocks and b rows into a
+// stage with cp.async.bulk (TMA engine) completing on an mbarrier, always
+// kStages-1 tiles ahead; the warp pulls its blocks into registers, refills the
+// stage at once, and does the per-point segmented reduction with warp
+// shuffles. No CTA-wide synchronisation exists after start-up, so an SM keeps
+// ~12 independent tile pipelines in flight. Every Jacobian block crosses HBM
+// exactly once per product.
+#ifndef CB200_STREAM_KERNELS_CUH_
+#define CB200_STREAM_KERNELS_CUH_
+
+#include "kernels.cuh"
+
+namespace cb200 {
+
+constexpr int kStreamWarps = 4;
+constexpr int kStreamThreads = kStreamWarps * 32;
+constexpr int kMetaBytes = (int)sizeof(TileMeta);
+static_assert(kTileObs == 32, "one lane per row");
+
+enum PointMode {
+  kModeSx = 0,    // y += F'(t - E v),  t = F x          S*x without the D_f^2 term
+  kModePseZ = 1,  // y += F'(E v),      t = F x          F'E (E'E)^-1 E'F x
+  kModeRhs = 2,   // y += F'(t - E v),  t = b            reduced right-hand side
+  kModeBack = 3   // y_e = v,           t = b - F x      back substitution
+};                // with u = sum_rows E' t and v = (E'E + D_e^2)^-1 u per point
+
+struct StreamArgs {
+  const double* E;          // [N x 6]
+  const double* F;          // [N x 18]
+  const double* b;          // [2N] (kModeRhs, kModeBack); may be null in BUILD (t = 0)
+  const TileMeta* tiles;
+  int num_tiles;
+  double* ete_inv;          // [P x 6] upper triangle of (E'E + D_e^2)^-1; written when BUILD
+  const double* De;         // [3P] or null (BUILD)
+  double* weights;          // [N x 3] or null (BUILD): W_r = I - E_r inverse(ete) E_r'
+  const double* x;          // [9C] camera vector (unused for kModeRhs)
+  double* yrep;             // nrep privatised camera accumulators, rep_stride apart
+  int nrep;
+  int rep_stride;
+  double* y_e;              // [3P] (kModeBack)
+  const int* done;          // device convergence flag; the kernel is a no-op when set
+};
+
+template <int MODE, bool BUILD>
+struct StreamLayout {
+  static constexpr bool kUsesB = (MODE == kModeRhs || MODE == kModeBack);
+  static constexpr bool kLoadsInv = !BUILD;
+  static constexpr int kStages = 2;
+  // per stage (every offset a multiple of 16 bytes)
+  static constexpr int kOffE = 0;
+  static constexpr int kOffF = kOffE + kTileObs * 48;
+  static constexpr int kOffMeta = kOffF + kTileObs * 144;
+  static constexpr int kOffInv = kOffMeta + kMetaBytes;
+  static constexpr int kOffB = kOffInv + (kLoadsInv ? kTileObs * 48 : 0);
+  static constexpr int kStageBytes = kOffB + (kUsesB ? kTileObs * 16 : 0);
+  // per warp: stages, then the 32 x 9 transposition scratch, then the barriers
+  static constexpr int kOffX = kStages * kStageBytes;
+  static constexpr int kOffBars = kOffX + 288 * 8;
+  static constexpr int kWarpBytes = kOffBars + 16 * ((kStages * 8 + 15) / 16);
+  static constexpr int kSmemBytes = kStreamWarps * kWarpBytes;
+};
+
+template <typename L>
+__device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, unsigned char* st, uint64_t* bar) {
+  const int4 h = __ldg(reinterpret_cast<const int4*>(a.tiles + t));  // r0, n, p0, np
+  const bool use_b = L::kUsesB && a.b != nullptr;
+  const uint32_t bytes = (uint32_t)h.y * 192u + (uint32_t)kMetaBytes +
+                         (L::kLoadsInv ? (uint32_t)h.w * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
+  mbar_expect_tx(bar, bytes);
+  bulk_g2s(st + L::kOffMeta, a.tiles + t, (uint32_t)kMetaBytes, bar);
+  bulk_g2s(st + L::kOffE, a.E + (size_t)h.x * 6, (uint32_t)h.y * 48u, bar);
+  bulk_g2s(st + L::kOffF, a.F + (size_t)h.x * 18, (uint32_t)h.y * 144u, bar);
+  if (L::kLoadsInv) bulk_g2s(st + L::kOffInv, a.ete_inv + (size_t)h.z * 6, (uint32_t)h.w * 48u, bar);
+  if (use_b) bulk_g2s(st + L::kOffB, a.b + (size_t)h.x * 2, (uint32_t)h.y * 16u, bar);
+}
+
+// inclusive segmented sum along the lanes; segments are lane ranges [head, tail]
+__device__ __forceinline__ double SegScan(double v, int lane, int head) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const double up = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane - d >= head) v += up;
+  }
+  return v;
+}
+
+template <int MODE, bool BUILD>
+__global__ void __launch_bounds__(kStreamThreads, 3)
+point_stream_kernel(const StreamArgs a) {
+  using L = StreamLayout<MODE, BUILD>;
+  static_assert(!BUILD || MODE == kModeRhs, "the E'E build rides on the rhs pass");
+  if (a.done != nullptr && *a.done != 0) return;
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  unsigned char* wsm = smem + warp * L::kWarpBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(wsm + L::kOffBars);
+  double* sXw = reinterpret_cast<double*>(wsm + L::kOffX);
+  // contiguous tile range of this warp
+  const int gw = blockIdx.x * kStreamWarps + warp;
+  const int GW = gridDim.x * kStreamWarps;
+  const int t_begin = (int)((long long)a.num_tiles * gw / GW);
+  const int t_end = (int)((long long)a.num_tiles * (gw + 1) / GW);
+  if (t_begin >= t_end) return;
+  if (lane == 0) {
+    for (int s = 0; s < L::kStages; ++s) mbar_init(full + s, 1);
+    for (int s = 0; s < L::kStages && t_begin + s < t_end; ++s)
+      IssueTile<L>(a, t_begin + s, wsm + s * L::kStageBytes, full + s);
+  }
+  __syncwarp();
+  double* yacc = a.yrep + (size_t)(gw % a.nrep) * a.rep_stride;
+
+  // x is gathered one tile ahead: the loads of tile i+1's camera 9-vectors are in
+  // flight while tile i is processed (lane l holds elements j*32 + l of the
+  // warp's 32 x 9 values, so consecutive lanes read consecutive doubles).
+  double xq[9];
+  auto gather_x = [&](const TileMeta* m) {
+    const int c_own = m->cam[lane];  // 0 for idle lanes
+#pragma unroll
+    for (int j = 0; j < 9; ++j) {
+      const int idx = j * 32 + lane;
+      const int o = idx / 9;
+      const int k = idx - 9 * o;
+      const int c = __shfl_sync(0xffffffffu, c_own, o);
+      xq[j] = __ldg(a.x + 9 * c + k);  // idle rows read camera 0: no select may sit on the load
+    }
+  };
+  if (MODE != kModeRhs) {
+    mbar_wait(full + 0, 0);
+    gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMeta));
+  }
+
+  for (int t = t_begin, i = 0; t < t_end; ++t, ++i) {
+    const int s = i % L::kStages;
+    unsigned char* st = wsm + s * L::kStageBytes;
+    mbar_wait(full + s, (i / L::kStages) & 1);
+    const TileMeta* m = reinterpret_cast<const TileMeta*>(st + L::kOffMeta);
+    const int r0 = m->r0, n = m->n, p0 = m->p0;
+    // ---- everything this lane needs from the stage goes to registers ----
+    double Ei[6], Fi[18];
+    double t0 = 0.0, t1 = 0.0;
+    const int cam = m->cam[lane];
+    const int seg = m->seg[lane];
+    const int pt = seg & 255, head = (seg >> 8) & 255, tail = (seg >> 16) & 255;
+    const bool active = lane < n;
+    const bool is_tail = active && lane == tail;
+    {
+      const double2* e2 = reinterpret_cast<const double2*>(st + L::kOffE) + lane * 3;
+      const double2* f2 = reinterpret_cast<const double2*>(st + L::kOffF) + lane * 9;
+#pragma unroll
+      // idle lanes (lane >= n) read stale stage bytes: each is its own segment, and
+      // nothing they compute is stored or scattered
+      for (int k = 0; k < 3; ++k) { const double2 v = e2[k]; Ei[2 * k] = v.x; Ei[2 * k + 1] = v.y; }
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { const double2 v = f2[k]; Fi[2 * k] = v.x; Fi[2 * k + 1] = v.y; }
+      if (L::kUsesB && a.b != nullptr) {
+        const double2 bb = reinterpret_cast<const double2*>(st + L::kOffB)[lane];
+        t0 = bb.x; t1 = bb.y;
+      }
+    }
+    double inv[6];
+    double de0 = 0.0, de1 = 0.0, de2 = 0.0;
+    if (is_tail) {
+      if (L::kLoadsInv) {
+        const double2* g = reinterpret_cast<const double2*>(st + L::kOffInv) + pt * 3;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { const double2 v = g[k]; inv[2 * k] = v.x; inv[2 * k + 1] = v.y; }
+      }
+      if (BUILD && a.De != nullptr) {
+        const double* d = a.De + 3 * (size_t)(p0 + pt);
+        de0 = __ldg(d); de1 = __ldg(d + 1); de2 = __ldg(d + 2);
+      }
+    }
+    if (MODE != kModeRhs) {
+#pragma unroll
+      for (int j = 0; j < 9; ++j) sXw[j * 32 + lane] = xq[j];  // park this tile's x values
+    }
+    __syncwarp();
+    // the stage is free: refill it with the tile kStages ahead
+    if (lane == 0 && t + L::kStages < t_end) IssueTile<L>(a, t + L::kStages, st, full + s);
+
+    // ---- t = F x; start the gather of the next tile ----
+    if (MODE != kModeRhs) {
+      if (t + 1 < t_end) {
+        const int s1 = (i + 1) % L::kStages;
+        mbar_wait(full + s1, ((i + 1) / L::kStages) & 1);
+        gather_x(reinterpret_cast<const TileMeta*>(wsm + s1 * L::kStageBytes + L::kOffMeta));
+      }
+      double f0 = 0.0, f1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const double xk = sXw[lane * 9 + k];
+        f0 += Fi[k] * xk;
+        f1 += Fi[9 + k] * xk;
+      }
+      if (MODE == kModeBack) { t0 -= f0; t1 -= f1; } else { t0 = f0; t1 = f1; }
+      __syncwarp();  // sXw is reused by the scatter below
+    }
+    // ---- u = sum over the point's rows of E_r' t_r (and of E_r'E_r) ----
+    double u0 = SegScan(Ei[0] * t0 + Ei[3] * t1, lane, head);
+    double u1 = SegScan(Ei[1] * t0 + Ei[4] * t1, lane, head);
+    double u2 = SegScan(Ei[2] * t0 + Ei[5] * t1, lane, head);
+    double c6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // adjugate inverse (Schur-Jacobi weights)
+    if (BUILD) {
+      double q[6];
+      q[0] = SegScan(Ei[0] * Ei[0] + Ei[3] * Ei[3], lane, head);
+      q[1] = SegScan(Ei[0] * Ei[1] + Ei[3] * Ei[4], lane, head);
+      q[2] = SegScan(Ei[0] * Ei[2] + Ei[3] * Ei[5], lane, head);
+      q[3] = SegScan(Ei[1] * Ei[1] + Ei[4] * Ei[4], lane, head);
+      q[4] = SegScan(Ei[1] * Ei[2] + Ei[4] * Ei[5], lane, head);
+      q[5] = SegScan(Ei[2] * Ei[2] + Ei[5] * Ei[5], lane, head);
+      if (is_tail) {
+        double mm[9] = {q[0], q[1], q[2], q[1], q[3], q[4], q[2], q[4], q[5]};
+        mm[0] += de0 * de0; mm[4] += de1 * de1; mm[8] += de2 * de2;
+        if (a.weights != nullptr) {
+          double c[9];
+          Inverse3x3(mm, c);
+          c6[0] = c[0]; c6[1] = c[1]; c6[2] = c[2]; c6[3] = c[4]; c6[4] = c[5]; c6[5] = c[8];
+        }
+        LltInverseUpper<3>(mm);
+        inv[0] = mm[0]; inv[1] = mm[1]; inv[2] = mm[2]; inv[3] = mm[4]; inv[4] = mm[5]; inv[5] = mm[8];
+        double2* g = reinterpret_cast<double2*>(a.ete_inv + (size_t)(p0 + pt) * 6);
+        g[0] = make_double2(inv[0], inv[1]);
+        g[1] = make_double2(inv[2], inv[3]);
+        g[2] = make_double2(inv[4], inv[5]);
+      }
+    }
+    // ---- v = inverse * u at the point's last row, then to all its rows ----
+    double v0 = 0.0, v1 = 0.0, v2 = 0.0;
+    if (is_tail) {
+      v0 = inv[0] * u0 + inv[1] * u1 + inv[2] * u2;
+      v1 = inv[1] * u0 + inv[3] * u1 + inv[4] * u2;
+      v2 = inv[2] * u0 + inv[4] * u1 + inv[5] * u2;
+      if (MODE == kModeBack) {
+        double* y = a.y_e + (size_t)(p0 + pt) * 3;
+        y[0] = v0; y[1] = v1; y[2] = v2;
+      }
+    }
+    if (MODE == kModeBack) continue;
+    v0 = __shfl_sync(0xffffffffu, v0, tail);
+    v1 = __shfl_sync(0xffffffffu, v1, tail);
+    v2 = __shfl_sync(0xffffffffu, v2, tail);
+    // ---- w_r = t_r - E_r v (or E_r v); F_r' w_r goes to the camera accumulator ----
+    {
+      const double ev0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2;
+      const double ev1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
+      const double w0 = (MODE == kModePseZ) ? ev0 : t0 - ev0;
+      const double w1 = (MODE == kModePseZ) ? ev1 : t1 - ev1;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) sXw[lane * 9 + k] = Fi[k] * w0 + Fi[9 + k] * w1;
+    }
+    if (BUILD && a.weights != nullptr) {
+      // W_r = I - E_r c E_r' with c the adjugate inverse (InvertPSDMatrix<3>)
+#pragma unroll
+      for (int k = 0; k < 6; ++k) c6[k] = __shfl_sync(0xffffffffu, c6[k], tail);
+      const double g00 = Ei[0] * c6[0] + Ei[1] * c6[1] + Ei[2] * c6[2];
+      const double g01 = Ei[0] * c6[1] + Ei[1] * c6[3] + Ei[2] * c6[4];
+      const double g02 = Ei[0] * c6[2] + Ei[1] * c6[4] + Ei[2] * c6[5];
+      const double g10 = Ei[3] * c6[0] + Ei[4] * c6[1] + Ei[5] * c6[2];
+      const double g11 = Ei[3] * c6[1] + Ei[4] * c6[3] + Ei[5] * c6[4];
+      const double g12 = Ei[3] * c6[2] + Ei[4] * c6[4] + Ei[5] * c6[5];
+      if (active) {
+        double* w = a.weights + (size_t)(r0 + lane) * 3;
+        w[0] = 1.0 - (g00 * Ei[0] + g01 * Ei[1] + g02 * Ei[2]);
+        w[1] = -(g00 * Ei[3] + g01 * Ei[4] + g02 * Ei[5]);
+        w[2] = 1.0 - (g10 * Ei[3] + g11 * Ei[4] + g12 * Ei[5]);
+      }
+    }
+    __syncwarp();
+    if (!(BUILD && a.b == nullptr)) {
+#pragma unroll
+      for (int j = 0; j < 9; ++j) {
+        const int idx = j * 32 + lane;
+        const int o = idx / 9;
+        const int k = idx - 9 * o;
+        const int c = __shfl_sync(0xffffffffu, cam, o);
+        if (o < n) atomicAdd(yacc + 9 * c + k, sXw[idx]);
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// Points without rows (legal in the block structure, absent from real bundle
+// adjustment programs): (E'E + D^2)^-1 = D^-2 and a zero back-substituted step.
+__global__ void empty_points_kernel(const int* __restrict__ empty_points, int count,
+                                    const double* __restrict__ De, double* __restrict__ ete_inv,
+                                    double* __restrict__ y_e) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const int p = empty_points[i];
+  if (ete_inv != nullptr) {
+    double mm[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (De != nullptr)
+      for (int k = 0; k < 3; ++k) mm[4 * k] = De[3 * (size_t)p + k] * De[3 * (size_t)p + k];
+    LltInverseUpper<3>(mm);
+    double* g = ete_inv + (size_t)p * 6;
+    g[0] = mm[0]; g[1] = mm[1]; g[2] = mm[2]; g[3] = mm[4]; g[4] = mm[5]; g[5] = mm[8];
+  }
+  if (y_e != nullptr) { y_e[3 * (size_t)p] = 0.0; y_e[3 * (size_t)p + 1] = 0.0; y_e[3 * (size_t)p + 2] = 0.0; }
+}
+
+// A point with more rows than a tile: one CTA walks its rows twice (the second
+// pass hits L2). grid = number of long points. Same modes as above.
+template <int MODE, bool BUILD>
+__global__ void __launch_bounds__(256)
+point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
+                  const int* __restrict__ row_start, const int* __restrict__ cam) {
+  if (a.done != nullptr && *a.done != 0) return;
+  __shared__ double sbuf[8];
+  const int p = long_points[blockIdx.x];
+  const int r0 = row_start[p], r1 = row_start[p + 1];
+  const bool use_b = (MODE == kModeRhs || MODE == kModeBack) && a.b != nullptr;
+  double u[3] = {0.0, 0.0, 0.0};
+  double q[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  for (int r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+    const double* Ei = a.E + (size_t)r * 6;
+    const double* Fi = a.F + (size_t)r * 18;
+    double t0 = 0.0, t1 = 0.0;
+    if (use_b) { t0 = a.b[2 * (size_t)r]; t1 = a.b[2 * (size_t)r + 1]; }
+    if (MODE != kModeRhs) {
+      const double* x = a.x + 9 * (size_t)cam[r];
+      double f0 = 0.0, f1 = 0.0;
+      for (int k = 0; k < 9; ++k) { f0 += Fi[k] * x[k]; f1 += Fi[9 + k] * x[k]; }
+      if (MODE == kModeBack) { t0 -= f0; t1 -= f1; } else { t0 = f0; t1 = f1; }
+    }
+    for (int k = 0; k < 3; ++k) u[k] += Ei[k] * t0 + Ei[3 + k] * t1;
+    if (BUILD) {
+      q[0] += Ei[0] * Ei[0] + Ei[3] * Ei[3];
+      q[1] += Ei[0] * Ei[1] + Ei[3] * Ei[4];
+      q[2] += Ei[0] * Ei[2] + Ei[3] * Ei[5];
+      q[3] += Ei[1] * Ei[1] + Ei[4] * Ei[4];
+      q[4] += Ei[1] * Ei[2] + Ei[4] * Ei[5];
+      q[5] += Ei[2] * Ei[2] + Ei[5] * Ei[5];
+    }
+  }
+  for (int k = 0; k < 3; ++k) u[k] = BlockSum(u[k], sbuf);
+  double inv[6], c[9];
+  if (BUILD) {
+    for (int k = 0; k < 6; ++k) q[k] = BlockSum(q[k], sbuf);
+    double mm[9] = {q[0], q[1], q[2], q[1], q[3], q[4], q[2], q[4], q[5]};
+    if (a.De != nullptr) {
+      const double* d = a.De + 3 * (size_t)p;
+      mm[0] += d[0] * d[0]; mm[4] += d[1] * d[1]; mm[8] += d[2] * d[2];
+    }
+    Inverse3x3(mm, c);
+    LltInverseUpper<3>(mm);
+    inv[0] = mm[0]; inv[1] = mm[1]; inv[2] = mm[2]; inv[3] = mm[4]; inv[4] = mm[5]; inv[5] = mm[8];
+    if (threadIdx.x == 0)
+      for (int k = 0; k < 6; ++k) a.ete_inv[(size_t)p * 6 + k] = inv[k];
+  } else {
+    for (int k = 0; k < 6; ++k) inv[k] = a.ete_inv[(size_t)p * 6 + k];
+  }
+  const double v0 = inv[0] * u[0] + inv[1] * u[1] + inv[2] * u[2];
+  const double v1 = inv[1] * u[0] + inv[3] * u[1] + inv[4] * u[2];
+  const double v2 = inv[2] * u[0] + inv[4] * u[1] + inv[5] * u[2];
+  if (MODE == kModeBack) {
+    if (threadIdx.x == 0) { a.y_e[3 * (size_t)p] = v0; a.y_e[3 * (size_t)p + 1] = v1; a.y_e[3 * (size_t)p + 2] = v2; }
+    return;
+  }
+  double* y = a.yrep + (size_t)(blockIdx.x % a.nrep) * a.rep_stride;
+  for (int r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+    const double* Ei = a.E + (size_t)r * 6;
+    const double* Fi = a.F + (size_t)r * 18;
+    if (BUILD && a.weights != nullptr) {
+      double g0[3], g1[3];
+      for (int j = 0; j < 3; ++j) {
+        g0[j] = Ei[0] * c[j] + Ei[1] * c[3 + j] + Ei[2] * c[6 + j];
+        g1[j] = Ei[3] * c[j] + Ei[4] * c[3 + j] + Ei[5] * c[6 + j];
+      }
+      double* w = a.weights + (size_t)r * 3;
+      w[0] = 1.0 - (g0[0] * Ei[0] + g0[1] * Ei[1] + g0[2] * Ei[2]);
+      w[1] = -(g0[0] * Ei[3] + g0[1] * Ei[4] + g0[2] * Ei[5]);
+      w[2] = 1.0 - (g1[0] * Ei[3] + g1[1] * Ei[4] + g1[2] * Ei[5]);
+    }
+    if (BUILD && a.b == nullptr) continue;
+    double t0 = 0.0, t1 = 0.0;
+    if (MODE == kModeRhs) { t0 = a.b[2 * (size_t)r]; t1 = a.b[2 * (size_t)r + 1]; }
+    else {
+      const double* x = a.x + 9 * (size_t)cam[r];
+      for (int k = 0; k < 9; ++k) { t0 += Fi[k] * x[k]; t1 += Fi[9 + k] * x[k]; }
+    }
+    const double ev0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2;
+    const double ev1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
+    const double w0 = (MODE == kModePseZ) ? ev0 : t0 - ev0;
+    const double w1 = (MODE == kModePseZ) ? ev1 : t1 - ev1;
+    double* yc = y + 9 * (size_t)cam[r];
+    for (int k = 0; k < 9; ++k) atomicAdd(yc + k, Fi[k] * w0 + Fi[9 + k] * w1);
+  }
+}
+
+// [P x 6] upper triangles -> [P x 9] full symmetric row-major blocks (seam output only)
+__global__ void expand_symmetric3_kernel(const double* __restrict__ in6, int P, double* __restrict__ out9) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const double* a = in6 + (size_t)p * 6;
+  double* o = out9 + (size_t)p * 9;
+  o[0] = a[0]; o[1] = a[1]; o[2] = a[2];
+  o[3] = a[1]; o[4] = a[3]; o[5] = a[4];
+  o[6] = a[2]; o[7] = a[4]; o[8] = a[5];
+}
+
+}  // namespace cb200
+#endif  // CB200_STREAM_KERNELS_CUH_
