@@ -284,6 +284,22 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   return CB200_OK;
 }
 
+int cb200_shard_plan(const cb200_structure* structure, int num_eliminate_blocks, int world_size,
+                     int* point_bounds, int* row_bounds) {
+  if (!structure || world_size < 1 || !point_bounds || !row_bounds)
+    return Fail(CB200_ERR_INVALID_ARGUMENT, "null argument or bad world_size");
+  FlatStructure flat;
+  std::string err;
+  const int rc = Flatten(*structure, num_eliminate_blocks, &flat, &err);
+  if (rc != CB200_OK) return Fail(rc, err);
+  const std::vector<int> bounds = ShardPoints(flat.point_row_start, world_size);
+  for (int g = 0; g <= world_size; ++g) {
+    point_bounds[g] = bounds[g];
+    row_bounds[g] = flat.point_row_start[bounds[g]];
+  }
+  return CB200_OK;
+}
+
 int cb200_num_rows(const cb200_solver* s) { return s ? 2 * s->N : 0; }
 int cb200_num_cols(const cb200_solver* s) { return s ? 3 * s->P + 9 * s->C : 0; }
 int cb200_num_cols_e(const cb200_solver* s) { return s ? 3 * s->P : 0; }

@@ -79,8 +79,8 @@ struct StreamLayout {
 };
 
 template <typename L>
-__device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, unsigned char* st, uint64_t* bar) {
-  const int4 h = __ldg(reinterpret_cast<const int4*>(a.tiles + t));  // r0, n, p0, np
+__device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, const int4 h /* r0, n, p0, np */,
+                                          unsigned char* st, uint64_t* bar) {
   const bool use_b = L::kUsesB && a.b != nullptr;
   const uint32_t bytes = (uint32_t)h.y * 192u + (uint32_t)kMetaBytes +
                          (L::kLoadsInv ? (uint32_t)h.w * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
@@ -97,7 +97,8 @@ __device__ __forceinline__ double SegScan(double v, int lane, int head) {
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const double up = __shfl_up_sync(0xffffffffu, v, d);
-    if (lane - d >= head) v += up;
+    asm("{\n .reg .pred p;\n setp.ge.s32 p, %2, %3;\n @p add.f64 %0, %0, %1;\n}"
+        : "+d"(v) : "d"(up), "r"(lane - d), "r"(head));
   }
   return v;
 }
@@ -120,10 +121,14 @@ point_stream_kernel(const StreamArgs a) {
   const int t_begin = (int)((long long)a.num_tiles * gw / GW);
   const int t_end = (int)((long long)a.num_tiles * (gw + 1) / GW);
   if (t_begin >= t_end) return;
+  // header of the tile to issue next, loaded one iteration before it is needed
+  int4 hnext = make_int4(0, 0, 0, 0);
   if (lane == 0) {
     for (int s = 0; s < L::kStages; ++s) mbar_init(full + s, 1);
     for (int s = 0; s < L::kStages && t_begin + s < t_end; ++s)
-      IssueTile<L>(a, t_begin + s, wsm + s * L::kStageBytes, full + s);
+      IssueTile<L>(a, t_begin + s, __ldg(reinterpret_cast<const int4*>(a.tiles + t_begin + s)),
+                   wsm + s * L::kStageBytes, full + s);
+    if (t_begin + L::kStages < t_end) hnext = __ldg(reinterpret_cast<const int4*>(a.tiles + t_begin + L::kStages));
   }
   __syncwarp();
   double* yacc = a.yrep + (size_t)(gw % a.nrep) * a.rep_stride;
@@ -140,7 +145,7 @@ point_stream_kernel(const StreamArgs a) {
       const int o = idx / 9;
       const int k = idx - 9 * o;
       const int c = __shfl_sync(0xffffffffu, c_own, o);
-      xq[j] = __ldg(a.x + 9 * c + k);  // idle rows read camera 0: no select may sit on the load
+      xq[j] = __ldg(a.x + c + k);  // idle rows read camera 0: no select may sit on the load
     }
   };
   if (MODE != kModeRhs) {
@@ -195,7 +200,10 @@ point_stream_kernel(const StreamArgs a) {
     }
     __syncwarp();
     // the stage is free: refill it with the tile kStages ahead
-    if (lane == 0 && t + L::kStages < t_end) IssueTile<L>(a, t + L::kStages, st, full + s);
+    if (lane == 0 && t + L::kStages < t_end) {
+      IssueTile<L>(a, t + L::kStages, hnext, st, full + s);
+      if (t + L::kStages + 1 < t_end) hnext = __ldg(reinterpret_cast<const int4*>(a.tiles + t + L::kStages + 1));
+    }
 
     // ---- t = F x; start the gather of the next tile ----
     if (MODE != kModeRhs) {
@@ -292,7 +300,7 @@ point_stream_kernel(const StreamArgs a) {
         const int o = idx / 9;
         const int k = idx - 9 * o;
         const int c = __shfl_sync(0xffffffffu, cam, o);
-        if (o < n) atomicAdd(yacc + 9 * c + k, sXw[idx]);
+        if (o < n) atomicAdd(yacc + c + k, sXw[idx]);
       }
     }
     __syncwarp();

@@ -58,6 +58,7 @@ SYMBOLS = {
     "cb200_num_cols_e": (ctypes.c_int, [_H]),
     "cb200_num_cols_f": (ctypes.c_int, [_H]),
     "cb200_shard": (ctypes.c_int, [_H, _ip, _ip, _ip, _ip]),
+    "cb200_shard_plan": (ctypes.c_int, [ctypes.POINTER(CStructure), ctypes.c_int, ctypes.c_int, _ip, _ip]),
     "cb200_solve": (ctypes.c_int, [_H, _dp, _dp, _dp, ctypes.c_double, ctypes.c_double, _dp,
                                    ctypes.POINTER(CSummary)]),
     "cb200_upload": (ctypes.c_int, [_H, _dp, _dp, _dp]),
@@ -331,6 +332,15 @@ class IterativeSchurComplementSolver:
         ms, n = ctypes.c_float(), ctypes.c_int()
         _check(self.L.cb200_time_op(self.h, op, warmup, iters, ctypes.byref(ms), ctypes.byref(n)))
         return ms.value, n.value
+
+
+def shard_plan(structure, world_size):
+    """(point_bounds, row_bounds), world_size + 1 entries each: the sharding cb200_create applies."""
+    pb = np.zeros(world_size + 1, dtype=np.int32)
+    rb = np.zeros(world_size + 1, dtype=np.int32)
+    cs = structure.c_struct()
+    _check(lib().cb200_shard_plan(ctypes.byref(cs), structure.num_eliminate_blocks, world_size, _i(pb), _i(rb)))
+    return pb, rb
 
 
 def nccl_unique_id():

@@ -117,6 +117,14 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
                  cb200_solver** out);
 void cb200_destroy(cb200_solver* s);
 
+/* The point sharding cb200_create applies, without a device (host only): rank g
+ * owns points [point_bounds[g], point_bounds[g+1]) and row blocks
+ * [row_bounds[g], row_bounds[g+1]); contiguous ranges of balanced observation
+ * count (the idea of PartitionRangeForParallelFor over cumulative_nnz,
+ * block_sparse_matrix.cc:58-67). Both outputs have world_size + 1 entries. */
+int cb200_shard_plan(const cb200_structure* structure, int num_eliminate_blocks, int world_size,
+                     int* point_bounds, int* row_bounds);
+
 /* sizes: num_cols = 3P + 9C (x), num_cols_f = 9C, num_rows = 2N. */
 int cb200_num_rows(const cb200_solver* s);
 int cb200_num_cols(const cb200_solver* s);

@@ -82,3 +82,23 @@ def test_synthetic_jacobian_is_the_derivative():
     assert util.rel_err(p.jacobian_times(values, x), J @ x) < 1e-13
     v2 = p.scale_columns(values.copy(), 1.0 / (1.0 + x * x))
     assert util.rel_err(util.oracle_structure(p.structure).dense(v2), J / (1.0 + x * x)) < 1e-13
+
+
+def test_adapter_header_flattens_a_ceres_block_structure(tmp_path):
+    """include/ceres_b200_adapter.h (the reference-side binding of INTEGRATION.md) compiled against a
+    stand-in for ceres/block_structure.h; the tile plan covers every row once; cb200_create is
+    reached through the C ABI from C++ (and refuses to run without a GPU)."""
+    import subprocess
+    m = util.pkg()
+    lib = m._build.build_cuda()
+    exe = str(tmp_path / "adapter_driver")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_driver.cc"),
+                    lib, "-Wl,-rpath," + os.path.dirname(lib)], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    kv = dict(t.split("=") for t in out.split())
+    assert kv["flatten"] == "0" and kv["canonical"] == "1" and kv["bad"] == "0", out
+    N = int(kv["N"])
+    assert int(kv["rows_in_tiles"]) == N - 45 and kv["long"] == "1" and kv["empty"] == "1", out
+    sh = [int(t) for t in kv["shard"].split(",")]
+    assert sh[0] == 0 and sh[3] == 40 and sh[0] <= sh[1] <= sh[2] <= sh[3], out
+    assert kv["create"] == ("0" if util.has_gpu() else "-3"), out
