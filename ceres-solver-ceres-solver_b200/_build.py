@@ -14,7 +14,7 @@ LIB_BAL = os.path.join(HERE, "libsynthetic_bal.so")
 LIB_LM = os.path.join(HERE, "libceres_b200_lm.so")
 
 _CUDA_SRC = ["c_api.cu", "c_api_solve.inc", "c_api_entry.inc", "kernels.cuh", "camera_kernels.cuh",
-             "cg_kernels.cuh", "stream_kernels.cuh", "solver_state.h", "flatten.h"]
+             "cg_kernels.cuh", "cg_step.cuh", "stream_kernels.cuh", "solver_state.h", "flatten.h"]
 
 
 def _stale(out, srcs):

@@ -8,11 +8,13 @@
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
 #include "camera_kernels.cuh"
 #include "cg_kernels.cuh"
+#include "cg_step.cuh"
 #include "kernels.cuh"
 #include "solver_state.h"
 #include "stream_kernels.cuh"
@@ -159,7 +161,7 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   s->nvec = 9 * s->C;
   s->vec_blocks = std::min(kMaxVecBlocks, Blocks(s->nvec, kVecThreads));
   s->nrep = o.y_replicas > 0 ? o.y_replicas : 8;
-  s->rep_stride = (s->nvec + 31) / 32 * 32;
+  s->rep_stride = (10 * s->C + 31) / 32 * 32;  // accumulators are padded to 10 doubles per camera
 
   auto cleanup_fail = [&](int code) { cb200_destroy(s); return code; };
 #define TRY(expr) do { int rc2_ = (expr); if (rc2_ != CB200_OK) return cleanup_fail(rc2_); } while (0)
@@ -248,6 +250,8 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   TRY(DeviceAlloc(s, &s->d_ftf_inv, (size_t)s->C * 81));
   TRY(DeviceAlloc(s, &s->d_yrep, (size_t)s->nrep * s->rep_stride));
   TRY(DeviceAlloc(s, &s->d_y_e, Pl * 3));
+  TRY(DeviceAlloc(s, &s->d_x10, (size_t)10 * s->C));
+  TRY_CUDA(cudaMemset(s->d_x10, 0, (size_t)10 * s->C * sizeof(double)));
   double** vecs[] = {&s->d_rhs, &s->d_x, &s->d_r, &s->d_p, &s->d_z, &s->d_q, &s->d_t1, &s->d_t2};
   for (double** v : vecs) TRY(DeviceAlloc(s, v, nv));
   TRY(DeviceAlloc(s, &s->d_rows, Nl * 2));
@@ -267,6 +271,15 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   SET_SMEM(kModeBack, false); SET_SMEM(kModeRhs, true);
 #undef SET_SMEM
 
+  {
+    // the fused PCG step needs all its CTAs co-resident (grid barrier)
+    int coop = 0, per_sm = 0;
+    TRY_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, o.device_id));
+    TRY_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_step_kernel<kStepNormal, 1>, kStepThreads, 0));
+    const int ctas = Blocks(s->C, kStepThreads);
+    s->fused_step_ok = coop != 0 && ctas <= per_sm * s->num_sms && ctas <= kMaxVecBlocks &&
+                       std::getenv("CB200_NO_FUSED_STEP") == nullptr;
+  }
   if (o.world_size > 1) {
     TRY(LoadNccl(&s->nccl));
     UniqueId id;

@@ -124,17 +124,16 @@ __global__ void duplicate_pair_kernel(const double* __restrict__ E, const double
 // block_random_access_diagonal_matrix.cc:90-100; AddDiagonalAndInvert for F'F,
 // implicit_schur_complement.cc:179-204). One thread per camera. `partial_in`
 // non-null: blocks already hold all-reduced upper triangles [C x 45] instead.
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(256)
 camera_block_finish_kernel(const double* __restrict__ chunk_partial,
                            const int* __restrict__ cam_chunk_start, int C,
                            double* __restrict__ upper /* C x 45 */) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  for (int k = 0; k < 45; ++k) {
-    double s = 0.0;
-    for (int ch = cam_chunk_start[c]; ch < cam_chunk_start[c + 1]; ++ch) s += chunk_partial[(size_t)ch * 45 + k];
-    upper[(size_t)c * 45 + k] = s;
-  }
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;  // one thread per (camera, entry)
+  if (i >= C * 45) return;
+  const int c = i / 45, k = i - 45 * c;
+  double s = 0.0;
+  for (int ch = cam_chunk_start[c]; ch < cam_chunk_start[c + 1]; ++ch) s += chunk_partial[(size_t)ch * 45 + k];
+  upper[i] = s;
 }
 
 __global__ void __launch_bounds__(64)

@@ -41,7 +41,8 @@ struct CgState {
   int reason;                  // CgReason
   int min_iterations, max_iterations;
   unsigned int ticket[4];
-  double partial[4][kMaxVecBlocks];
+  unsigned int bar_count, bar_flag;  // grid barrier of cg_step_kernel (both 0 between launches)
+  double partial[6][kMaxVecBlocks];
 };
 
 __device__ __forceinline__ bool IsZeroOrInfinity(double x) { return x == 0.0 || isinf(x); }
@@ -158,11 +159,13 @@ cg_rho_kernel(CgState* st, const double* __restrict__ blocks, const double* __re
 
 // p = z (first iteration) or p = z + beta p (:173-188).
 __global__ void cg_update_p_kernel(const CgState* st, const double* __restrict__ z,
-                                   double* __restrict__ p, int n) {
+                                   double* __restrict__ p, double* __restrict__ p10, int n) {
   if (st->done) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  p[i] = (st->iter == 1) ? z[i] : z[i] + st->beta * p[i];
+  const double pi = (st->iter == 1) ? z[i] : z[i] + st->beta * p[i];
+  p[i] = pi;
+  p10[i + i / 9] = pi;  // the padded copy S*p gathers from
 }
 
 // q = sum of the privatised accumulators (which are re-zeroed for the next use).
@@ -173,13 +176,19 @@ __global__ void reduce_replicas_kernel(const int* done, double* __restrict__ yre
   if (done != nullptr && *done) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  const int c = i / 9;
   double s = 0.0;
-  for (int rep = 0; rep < nrep; ++rep) {
-    double* y = yrep + (size_t)rep * rep_stride + i;
-    s += *y;
-    *y = 0.0;
-  }
+  for (int rep = 0; rep < nrep; ++rep) s += __ldcg(yrep + (size_t)rep * rep_stride + i + c);  // 10 per camera
+  for (int rep = 0; rep < nrep; ++rep) yrep[(size_t)rep * rep_stride + i + c] = 0.0;
   q[i] = s;
+}
+
+// x [9C] -> x10 [10C]: camera vectors are gathered with 16-byte loads, which need
+// 16-byte aligned 9-vectors (the 10th double is never read as data).
+__global__ void pad10_kernel(const int* done, const double* __restrict__ x, double* __restrict__ x10, int n) {
+  if (done != nullptr && *done) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) x10[i + i / 9] = x[i];
 }
 
 // y = D_f^2 x + q  (implicit_schur_complement.cc:130-143), in place on q.

@@ -1,0 +1,263 @@
+// One cooperative kernel per PCG iteration for the camera-sized vector work of
+// ConjugateGradientsSolver (conjugate_gradients_solver.h:159-300) when the
+// preconditioner is the identity or a 9x9 block diagonal (JACOBI, SCHUR_JACOBI):
+// the fold of the S*p accumulators, the D_f^2 term, p'q, alpha, the x and r
+// updates, Q1, |r|, every termination test, z = M^-1 r, rho, beta and the new p
+// -- the "epilogue" of S*p fused with the "prologue" of the next S*p. One thread
+// owns one camera (9 entries of every vector, one 9x9 block); the two scalar
+// reductions per iteration go through per-CTA partials summed in index order by
+// every CTA (deterministic, identical decisions everywhere) behind a grid
+// barrier. Launched with cudaLaunchCooperativeKernel (all CTAs co-resident).
+#ifndef CB200_CG_STEP_CUH_
+#define CB200_CG_STEP_CUH_
+
+#include "cg_kernels.cuh"
+
+namespace cb200 {
+
+constexpr int kStepThreads = 128;
+
+enum CgStepKind {
+  kStepStart = 0,   // iteration 1 prologue: z = M^-1 r, rho, p = z          (:160-174)
+  kStepNormal = 1,  // epilogue of iteration i + prologue of iteration i+1    (:190-300,160-188)
+  kStepResetA = 2,  // residual-reset iteration, first half: pq, alpha, x     (:190-216)
+  kStepResetB = 3   // second half: r = rhs - S x, tests, prologue of i+1     (:221-300,160-188)
+};
+
+struct CgStepArgs {
+  CgState* st;
+  const double* blocks;  // [C x 81] inverted preconditioner blocks (PRECOND 1)
+  const double* Df;      // [9C] or null
+  const double* rhs;
+  double* x;
+  double* r;
+  double* p;
+  double* x10;           // [10C] padded copy of the vector the next S* multiplies
+  const double* q;       // [9C] S*p without D_f^2 when the fold was done elsewhere (multi-GPU), else null
+  double* yrep;          // accumulators of the per-point kernel (10 per camera), folded and zeroed here
+  int nrep;
+  int rep_stride;
+  int C;
+  double* trace;
+  int max_trace;
+};
+
+// Sense-reversing grid barrier on two ints of CgState. Two barriers per launch
+// bring the flag back to 0. Requires co-resident CTAs (cooperative launch).
+__device__ __forceinline__ void GridBarrier(CgState* st, int sense) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int old = atomicAdd(&st->bar_count, 1u);
+    if (old == gridDim.x - 1) {
+      st->bar_count = 0;
+      __threadfence();
+      atomicExch(&st->bar_flag, (unsigned int)sense);
+    } else {
+      while (*reinterpret_cast<volatile unsigned int*>(&st->bar_flag) != (unsigned int)sense) {}
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+// Block partials -> grid barrier -> every CTA sums all partials in index order.
+// `row0` selects the rows of CgState::partial: the two reductions of one launch
+// use different rows, so a fast CTA cannot overwrite what a slow one still reads.
+template <int K>
+__device__ __forceinline__ void GridSums(CgState* st, int sense, int row0, const double* vals,
+                                         double* sums, double* sbuf) {
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const double s = BlockSum(vals[k], sbuf);
+    if (threadIdx.x == 0) st->partial[row0 + k][blockIdx.x] = s;
+  }
+  GridBarrier(st, sense);
+  if (threadIdx.x < K) {
+    double s = 0.0;
+    const volatile double* part = st->partial[row0 + threadIdx.x];
+    for (unsigned int b = 0; b < gridDim.x; ++b) s += part[b];
+    sums[threadIdx.x] = s;
+  }
+  __syncthreads();
+}
+
+template <int KIND, int PRECOND>
+__global__ void __launch_bounds__(kStepThreads)
+cg_step_kernel(const CgStepArgs a) {
+  CgState* st = a.st;
+  if (st->done) return;
+  __shared__ double sbuf[8];
+  __shared__ double sums[4];
+  // scalars of the iteration, read before anything is written (CTA 0 writes after barrier 1)
+  const int it = st->iter;
+  double rho = st->rho;
+  double Q0 = st->Q0;
+  const double q_tol = st->q_tolerance, tol_r = st->tol_r;
+  const int min_it = st->min_iterations, max_it = st->max_iterations;
+  const bool writer = blockIdx.x == 0 && threadIdx.x == 0;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool on = c < a.C;
+  const size_t o9 = (size_t)c * 9, o10 = (size_t)c * 10;
+
+  double p[9], q[9], x[9], r[9], z[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) { p[k] = 0.0; q[k] = 0.0; x[k] = 0.0; r[k] = 0.0; z[k] = 0.0; }
+  double alpha = 0.0;
+
+  if (KIND != kStepStart) {
+    // ---- fold the accumulators: q = F'(..) of the multiplied vector ----
+    if (on) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { p[k] = a.p[o9 + k]; x[k] = a.x[o9 + k]; }
+      if (a.q != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[k] = a.q[o9 + k];
+      } else {
+        // all loads first (independent, pipelined), the zeroing stores afterwards:
+        // interleaving them serialises one L2 round trip per element
+        for (int rep = 0; rep < a.nrep; ++rep) {
+          const double* y = a.yrep + (size_t)rep * a.rep_stride + o10;
+#pragma unroll
+          for (int k = 0; k < 5; ++k) {
+            const double2 v = __ldcg(reinterpret_cast<const double2*>(y) + k);
+            q[2 * k] += v.x;
+            if (k < 4) q[2 * k + 1] += v.y;
+          }
+        }
+        for (int rep = 0; rep < a.nrep; ++rep) {
+          double2* y = reinterpret_cast<double2*>(a.yrep + (size_t)rep * a.rep_stride + o10);
+#pragma unroll
+          for (int k = 0; k < 5; ++k) y[k] = make_double2(0.0, 0.0);
+        }
+      }
+      // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
+      if (a.Df != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) { const double d = a.Df[o9 + k]; q[k] += d * d * (KIND == kStepResetB ? x[k] : p[k]); }
+      }
+    }
+  }
+  if (KIND == kStepNormal || KIND == kStepResetA) {
+    // ---- pq, alpha (:190-214) ----
+    double v[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { v[0] += p[k] * q[k]; v[1] += p[k] * p[k]; v[2] += q[k] * q[k]; }
+    GridSums<3>(st, 1, 0, v, sums, sbuf);
+    const double pq = sums[0];
+    if (pq <= 0.0 || isinf(pq)) {
+      if (writer) {
+        st->pq = pq; st->norm_p = sqrt(sums[1]); st->norm_q = sqrt(sums[2]);
+        Finish(st, CB200_LINEAR_SOLVER_NO_CONVERGENCE, kReasonIndefinite);
+      }
+      GridBarrier(st, 0);
+      return;
+    }
+    alpha = rho / pq;
+    if (writer) { st->pq = pq; st->alpha = alpha; }
+    if (isinf(alpha)) {
+      if (writer) Finish(st, CB200_LINEAR_SOLVER_FAILURE, kReasonAlphaFailure);
+      GridBarrier(st, 0);
+      return;
+    }
+    // ---- x += alpha p (:216) ----
+    if (on) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        x[k] += alpha * p[k];
+        a.x[o9 + k] = x[k];
+        if (a.trace != nullptr && it <= a.max_trace) a.trace[(size_t)(it - 1) * 9 * a.C + o9 + k] = x[k];
+        if (KIND == kStepResetA) a.x10[o10 + k] = x[k];  // S x comes next
+      }
+    }
+    if (KIND == kStepResetA) {
+      GridBarrier(st, 0);
+      return;
+    }
+  }
+  // ---- residual (:221-227) ----
+  if (on) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      if (KIND == kStepNormal) r[k] = a.r[o9 + k] - alpha * q[k];
+      else if (KIND == kStepResetB) r[k] = a.rhs[o9 + k] - q[k];
+      else r[k] = a.r[o9 + k];
+      if (KIND != kStepStart) a.r[o9 + k] = r[k];
+    }
+    // ---- z = M^-1 r (:160-161) ----
+    if (PRECOND == 0) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) z[k] = r[k];
+    } else {
+      const double* B = a.blocks + (size_t)c * 81;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) s += __ldg(B + i * 9 + k) * r[k];
+        z[i] = s;
+      }
+    }
+  }
+  double v[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    v[0] += r[k] * z[k];
+    if (KIND != kStepStart && on) { v[1] += x[k] * (a.rhs[o9 + k] + r[k]); v[2] += r[k] * r[k]; }
+  }
+  // kinds without the p'q reduction run this one as their first barrier and close with a third
+  constexpr bool kTailBarrier = (KIND == kStepStart || KIND == kStepResetB);
+  GridSums<3>(st, kTailBarrier ? 1 : 0, 3, v, sums, sbuf);
+  int next_it = it;
+  if (KIND != kStepStart) {
+    // ---- Q1, zeta, |r|, iteration limit (:229-300) ----
+    const double Q1 = -sums[1];
+    const double norm_r = sqrt(sums[2]);
+    const double zeta = it * (Q1 - Q0) / Q1;
+    int term = -1, reason = 0;
+    if (zeta < q_tol && it >= min_it) { term = CB200_LINEAR_SOLVER_SUCCESS; reason = kReasonZetaConvergence; }
+    else if (norm_r <= tol_r && it >= min_it) { term = CB200_LINEAR_SOLVER_SUCCESS; reason = kReasonResidualConvergence; }
+    else if (it >= max_it) { term = CB200_LINEAR_SOLVER_NO_CONVERGENCE; reason = kReasonMaxIterations; }
+    if (writer) {
+      st->Q1 = Q1; st->norm_r = norm_r; st->zeta = zeta;
+      if (reason != kReasonZetaConvergence) st->Q0 = Q1;
+      if (term >= 0) Finish(st, term, reason);
+    }
+    if (term >= 0) {
+      if (kTailBarrier) GridBarrier(st, 0);
+      return;
+    }
+  }
+  // ---- prologue of the next iteration: rho, beta, p (:163-188) ----
+  next_it = it + 1;
+  const double last_rho = rho;
+  rho = sums[0];
+  double beta = 0.0;
+  int fail = 0;
+  if (IsZeroOrInfinity(rho)) fail = kReasonRhoFailure;
+  else if (next_it > 1) {
+    beta = rho / last_rho;
+    if (IsZeroOrInfinity(beta)) fail = kReasonBetaFailure;
+  }
+  if (writer) {
+    st->iter = next_it; st->last_rho = last_rho; st->rho = rho;
+    if (next_it > 1 && fail != kReasonRhoFailure) st->beta = beta;
+    if (fail) Finish(st, CB200_LINEAR_SOLVER_FAILURE, fail);
+  }
+  if (fail) {
+    if (kTailBarrier) GridBarrier(st, 0);
+    return;
+  }
+  if (on) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const double pk = (next_it == 1) ? z[k] : z[k] + beta * p[k];
+      a.p[o9 + k] = pk;
+      a.x10[o10 + k] = pk;  // S p comes next
+    }
+  }
+  if (kTailBarrier) GridBarrier(st, 0);  // leave the barrier flag at 0 for the next launch
+}
+
+}  // namespace cb200
+#endif  // CB200_CG_STEP_CUH_

@@ -124,7 +124,7 @@ inline std::vector<int> ShardPoints(const std::vector<int>& point_row_start, int
 // side-band the device streams next to the Jacobian blocks (one bulk copy).
 struct alignas(16) TileMeta {
   int r0, n, p0, np;
-  int cam[kTileObs];   // 9 * camera of each row (offset into a camera vector)
+  int cam[kTileObs];   // 10 * camera of each row (offset into a camera vector padded to 10 per camera)
   int seg[kTileObs];   // tile-local point | first lane of the point << 8 | last lane << 16
 };
 static_assert(sizeof(TileMeta) % 16 == 0, "bulk copies move multiples of 16 bytes");
@@ -153,7 +153,7 @@ inline TilePlan PlanTiles(const int* row_start /* local, P_loc+1 */, const int* 
     for (int p : members) {
       const int first = row_start[p] - m.r0, last = row_start[p + 1] - 1 - m.r0;
       for (int l = first; l <= last; ++l) {
-        m.cam[l] = 9 * cam[m.r0 + l];
+        m.cam[l] = 10 * cam[m.r0 + l];
         m.seg[l] = (p - p0) | (first << 8) | (last << 16);
       }
     }

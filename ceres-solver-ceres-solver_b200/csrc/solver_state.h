@@ -42,6 +42,7 @@ struct cb200_solver {
   int num_sms = 0;        // persistent grids are sized in multiples of it
   bool has_D = false, values_resident = false, b_resident = false, isc_ready = false;
   bool sj_ready = false;
+  bool fused_step_ok = false;  // cg_step_kernel fits the device as one co-resident grid
 
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[8] = {};
@@ -59,6 +60,7 @@ struct cb200_solver {
   double *d_ete_inv = nullptr, *d_weights = nullptr, *d_chunk_partial = nullptr, *d_upper = nullptr;
   double *d_dup_blocks = nullptr, *d_sj = nullptr, *d_ftf_inv = nullptr;
   double *d_yrep = nullptr, *d_y_e = nullptr, *d_ete9 = nullptr;
+  double* d_x10 = nullptr;  // the vector being multiplied, padded to 10 doubles per camera (16-byte gathers)
   // device: camera vectors
   double *d_rhs = nullptr, *d_x = nullptr, *d_r = nullptr, *d_p = nullptr, *d_z = nullptr, *d_q = nullptr;
   double *d_t1 = nullptr, *d_t2 = nullptr, *d_rows = nullptr, *d_pts = nullptr;

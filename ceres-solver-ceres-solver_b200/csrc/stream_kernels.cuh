@@ -51,8 +51,8 @@ struct StreamArgs {
   double* ete_inv;          // [P x 6] upper triangle of (E'E + D_e^2)^-1; written when BUILD
   const double* De;         // [3P] or null (BUILD)
   double* weights;          // [N x 3] or null (BUILD): W_r = I - E_r inverse(ete) E_r'
-  const double* x;          // [9C] camera vector (unused for kModeRhs)
-  double* yrep;             // nrep privatised camera accumulators, rep_stride apart
+  const double* x;          // [10C] camera vector padded to 10 per camera (unused for kModeRhs)
+  double* yrep;             // nrep privatised camera accumulators (10 per camera), rep_stride apart
   int nrep;
   int rep_stride;
   double* y_e;              // [3P] (kModeBack)
@@ -71,34 +71,51 @@ struct StreamLayout {
   static constexpr int kOffInv = kOffMeta + kMetaBytes;
   static constexpr int kOffB = kOffInv + (kLoadsInv ? kTileObs * 48 : 0);
   static constexpr int kStageBytes = kOffB + (kUsesB ? kTileObs * 16 : 0);
-  // per warp: stages, then the 32 x 9 transposition scratch, then the barriers
+  // per warp: stages, then the 32 x 10 transposition scratch, then the barriers
   static constexpr int kOffX = kStages * kStageBytes;
-  static constexpr int kOffBars = kOffX + 288 * 8;
+  static constexpr int kOffBars = kOffX + 320 * 8;
   static constexpr int kWarpBytes = kOffBars + 16 * ((kStages * 8 + 15) / 16);
   static constexpr int kSmemBytes = kStreamWarps * kWarpBytes;
 };
 
 template <typename L>
 __device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, const int4 h /* r0, n, p0, np */,
-                                          unsigned char* st, uint64_t* bar) {
+                                          unsigned char* st, uint64_t* bar, uint64_t stream_policy) {
   const bool use_b = L::kUsesB && a.b != nullptr;
   const uint32_t bytes = (uint32_t)h.y * 192u + (uint32_t)kMetaBytes +
                          (L::kLoadsInv ? (uint32_t)h.w * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
   mbar_expect_tx(bar, bytes);
   bulk_g2s(st + L::kOffMeta, a.tiles + t, (uint32_t)kMetaBytes, bar);
-  bulk_g2s(st + L::kOffE, a.E + (size_t)h.x * 6, (uint32_t)h.y * 48u, bar);
-  bulk_g2s(st + L::kOffF, a.F + (size_t)h.x * 18, (uint32_t)h.y * 144u, bar);
+  // Jacobian blocks and b are read once per pass: first in line for eviction
+  bulk_g2s_hint(st + L::kOffE, a.E + (size_t)h.x * 6, (uint32_t)h.y * 48u, bar, stream_policy);
+  bulk_g2s_hint(st + L::kOffF, a.F + (size_t)h.x * 18, (uint32_t)h.y * 144u, bar, stream_policy);
   if (L::kLoadsInv) bulk_g2s(st + L::kOffInv, a.ete_inv + (size_t)h.z * 6, (uint32_t)h.w * 48u, bar);
-  if (use_b) bulk_g2s(st + L::kOffB, a.b + (size_t)h.x * 2, (uint32_t)h.y * 16u, bar);
+  if (use_b) bulk_g2s_hint(st + L::kOffB, a.b + (size_t)h.x * 2, (uint32_t)h.y * 16u, bar, stream_policy);
 }
 
-// inclusive segmented sum along the lanes; segments are lane ranges [head, tail]
-__device__ __forceinline__ double SegScan(double v, int lane, int head) {
+// Tile header (r0, n, p0, np). volatile asm: the compiler must keep the value in
+// registers across the loop iteration instead of re-issuing the load where it is used.
+__device__ __forceinline__ int4 LoadHeader(const TileMeta* t) {
+  int4 h;
+  asm volatile("ld.global.nc.v4.s32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(h.x), "=r"(h.y), "=r"(h.z), "=r"(h.w) : "l"(t));
+  return h;
+}
+
+// Inclusive segmented sum along the lanes; segments are lane ranges [head, tail].
+// mask[s] is 1.0 where lane - 2^s >= head, else 0.0: one DFMA per step and value.
+struct SegMask { double m[5]; };
+__device__ __forceinline__ SegMask MakeSegMask(int lane, int head) {
+  SegMask k;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const double up = __shfl_up_sync(0xffffffffu, v, d);
-    asm("{\n .reg .pred p;\n setp.ge.s32 p, %2, %3;\n @p add.f64 %0, %0, %1;\n}"
-        : "+d"(v) : "d"(up), "r"(lane - d), "r"(head));
+  for (int s = 0; s < 5; ++s) k.m[s] = (lane - (1 << s) >= head) ? 1.0 : 0.0;
+  return k;
+}
+__device__ __forceinline__ double SegScan(double v, const SegMask& k) {
+#pragma unroll
+  for (int s = 0; s < 5; ++s) {
+    const double up = __shfl_up_sync(0xffffffffu, v, 1 << s);
+    v = fma(up, k.m[s], v);
   }
   return v;
 }
@@ -123,29 +140,31 @@ point_stream_kernel(const StreamArgs a) {
   if (t_begin >= t_end) return;
   // header of the tile to issue next, loaded one iteration before it is needed
   int4 hnext = make_int4(0, 0, 0, 0);
+  const uint64_t stream_policy = policy_evict_first();
   if (lane == 0) {
     for (int s = 0; s < L::kStages; ++s) mbar_init(full + s, 1);
     for (int s = 0; s < L::kStages && t_begin + s < t_end; ++s)
-      IssueTile<L>(a, t_begin + s, __ldg(reinterpret_cast<const int4*>(a.tiles + t_begin + s)),
-                   wsm + s * L::kStageBytes, full + s);
-    if (t_begin + L::kStages < t_end) hnext = __ldg(reinterpret_cast<const int4*>(a.tiles + t_begin + L::kStages));
+      IssueTile<L>(a, t_begin + s, LoadHeader(a.tiles + t_begin + s),
+                   wsm + s * L::kStageBytes, full + s, stream_policy);
+    if (t_begin + L::kStages < t_end) hnext = LoadHeader(a.tiles + t_begin + L::kStages);
   }
   __syncwarp();
   double* yacc = a.yrep + (size_t)(gw % a.nrep) * a.rep_stride;
 
   // x is gathered one tile ahead: the loads of tile i+1's camera 9-vectors are in
-  // flight while tile i is processed (lane l holds elements j*32 + l of the
-  // warp's 32 x 9 values, so consecutive lanes read consecutive doubles).
-  double xq[9];
+  // flight while tile i is processed. Camera vectors are padded to 10 doubles, so
+  // the warp's 32 x 10 values are 160 aligned 16-byte pieces: lane l loads pieces
+  // j*32 + l (consecutive lanes read consecutive pieces of a camera).
+  double2 xq[5];
   auto gather_x = [&](const TileMeta* m) {
-    const int c_own = m->cam[lane];  // 0 for idle lanes
+    const int c_own = m->cam[lane];  // 10 * camera; 0 for idle lanes (no select may sit on the loads)
 #pragma unroll
-    for (int j = 0; j < 9; ++j) {
+    for (int j = 0; j < 5; ++j) {
       const int idx = j * 32 + lane;
-      const int o = idx / 9;
-      const int k = idx - 9 * o;
+      const int o = idx / 5;
+      const int h = idx - 5 * o;
       const int c = __shfl_sync(0xffffffffu, c_own, o);
-      xq[j] = __ldg(a.x + c + k);  // idle rows read camera 0: no select may sit on the load
+      xq[j] = __ldg(reinterpret_cast<const double2*>(a.x + c) + h);
     }
   };
   if (MODE != kModeRhs) {
@@ -196,13 +215,13 @@ point_stream_kernel(const StreamArgs a) {
     }
     if (MODE != kModeRhs) {
 #pragma unroll
-      for (int j = 0; j < 9; ++j) sXw[j * 32 + lane] = xq[j];  // park this tile's x values
+      for (int j = 0; j < 5; ++j) reinterpret_cast<double2*>(sXw)[j * 32 + lane] = xq[j];  // park this tile's x
     }
     __syncwarp();
     // the stage is free: refill it with the tile kStages ahead
     if (lane == 0 && t + L::kStages < t_end) {
-      IssueTile<L>(a, t + L::kStages, hnext, st, full + s);
-      if (t + L::kStages + 1 < t_end) hnext = __ldg(reinterpret_cast<const int4*>(a.tiles + t + L::kStages + 1));
+      IssueTile<L>(a, t + L::kStages, hnext, st, full + s, stream_policy);
+      if (t + L::kStages + 1 < t_end) hnext = LoadHeader(a.tiles + t + L::kStages + 1);
     }
 
     // ---- t = F x; start the gather of the next tile ----
@@ -212,29 +231,38 @@ point_stream_kernel(const StreamArgs a) {
         mbar_wait(full + s1, ((i + 1) / L::kStages) & 1);
         gather_x(reinterpret_cast<const TileMeta*>(wsm + s1 * L::kStageBytes + L::kOffMeta));
       }
-      double f0 = 0.0, f1 = 0.0;
+      double xr[10];
 #pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        const double xk = sXw[lane * 9 + k];
-        f0 += Fi[k] * xk;
-        f1 += Fi[9 + k] * xk;
+      for (int k = 0; k < 5; ++k) {
+        const double2 v = reinterpret_cast<const double2*>(sXw)[lane * 5 + k];
+        xr[2 * k] = v.x; xr[2 * k + 1] = v.y;
       }
+      // two chains per output row halve the dependent-DFMA depth
+      double f0 = Fi[0] * xr[0], f0b = Fi[1] * xr[1], f1 = Fi[9] * xr[0], f1b = Fi[10] * xr[1];
+#pragma unroll
+      for (int k = 2; k < 8; k += 2) {
+        f0 = fma(Fi[k], xr[k], f0); f0b = fma(Fi[k + 1], xr[k + 1], f0b);
+        f1 = fma(Fi[9 + k], xr[k], f1); f1b = fma(Fi[10 + k], xr[k + 1], f1b);
+      }
+      f0 = fma(Fi[8], xr[8], f0) + f0b;
+      f1 = fma(Fi[17], xr[8], f1) + f1b;
       if (MODE == kModeBack) { t0 -= f0; t1 -= f1; } else { t0 = f0; t1 = f1; }
       __syncwarp();  // sXw is reused by the scatter below
     }
     // ---- u = sum over the point's rows of E_r' t_r (and of E_r'E_r) ----
-    double u0 = SegScan(Ei[0] * t0 + Ei[3] * t1, lane, head);
-    double u1 = SegScan(Ei[1] * t0 + Ei[4] * t1, lane, head);
-    double u2 = SegScan(Ei[2] * t0 + Ei[5] * t1, lane, head);
+    const SegMask km = MakeSegMask(lane, head);
+    double u0 = SegScan(Ei[0] * t0 + Ei[3] * t1, km);
+    double u1 = SegScan(Ei[1] * t0 + Ei[4] * t1, km);
+    double u2 = SegScan(Ei[2] * t0 + Ei[5] * t1, km);
     double c6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // adjugate inverse (Schur-Jacobi weights)
     if (BUILD) {
       double q[6];
-      q[0] = SegScan(Ei[0] * Ei[0] + Ei[3] * Ei[3], lane, head);
-      q[1] = SegScan(Ei[0] * Ei[1] + Ei[3] * Ei[4], lane, head);
-      q[2] = SegScan(Ei[0] * Ei[2] + Ei[3] * Ei[5], lane, head);
-      q[3] = SegScan(Ei[1] * Ei[1] + Ei[4] * Ei[4], lane, head);
-      q[4] = SegScan(Ei[1] * Ei[2] + Ei[4] * Ei[5], lane, head);
-      q[5] = SegScan(Ei[2] * Ei[2] + Ei[5] * Ei[5], lane, head);
+      q[0] = SegScan(Ei[0] * Ei[0] + Ei[3] * Ei[3], km);
+      q[1] = SegScan(Ei[0] * Ei[1] + Ei[3] * Ei[4], km);
+      q[2] = SegScan(Ei[0] * Ei[2] + Ei[3] * Ei[5], km);
+      q[3] = SegScan(Ei[1] * Ei[1] + Ei[4] * Ei[4], km);
+      q[4] = SegScan(Ei[1] * Ei[2] + Ei[4] * Ei[5], km);
+      q[5] = SegScan(Ei[2] * Ei[2] + Ei[5] * Ei[5], km);
       if (is_tail) {
         double mm[9] = {q[0], q[1], q[2], q[1], q[3], q[4], q[2], q[4], q[5]};
         mm[0] += de0 * de0; mm[4] += de1 * de1; mm[8] += de2 * de2;
@@ -345,7 +373,7 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
     double t0 = 0.0, t1 = 0.0;
     if (use_b) { t0 = a.b[2 * (size_t)r]; t1 = a.b[2 * (size_t)r + 1]; }
     if (MODE != kModeRhs) {
-      const double* x = a.x + 9 * (size_t)cam[r];
+      const double* x = a.x + 10 * (size_t)cam[r];
       double f0 = 0.0, f1 = 0.0;
       for (int k = 0; k < 9; ++k) { f0 += Fi[k] * x[k]; f1 += Fi[9 + k] * x[k]; }
       if (MODE == kModeBack) { t0 -= f0; t1 -= f1; } else { t0 = f0; t1 = f1; }
@@ -403,14 +431,14 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
     double t0 = 0.0, t1 = 0.0;
     if (MODE == kModeRhs) { t0 = a.b[2 * (size_t)r]; t1 = a.b[2 * (size_t)r + 1]; }
     else {
-      const double* x = a.x + 9 * (size_t)cam[r];
+      const double* x = a.x + 10 * (size_t)cam[r];
       for (int k = 0; k < 9; ++k) { t0 += Fi[k] * x[k]; t1 += Fi[9 + k] * x[k]; }
     }
     const double ev0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2;
     const double ev1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
     const double w0 = (MODE == kModePseZ) ? ev0 : t0 - ev0;
     const double w1 = (MODE == kModePseZ) ? ev1 : t1 - ev1;
-    double* yc = y + 9 * (size_t)cam[r];
+    double* yc = y + 10 * (size_t)cam[r];
     for (int k = 0; k < 9; ++k) atomicAdd(yc + k, Fi[k] * w0 + Fi[9 + k] * w1);
   }
 }

@@ -48,7 +48,7 @@ int main(int argc, char** argv) {
       const int pt = t.seg[l] & 255, head = (t.seg[l] >> 8) & 255, tail = (t.seg[l] >> 16) & 255;
       const int p = t.p0 + pt;
       if (fs.point_row_start[p] != t.r0 + head || fs.point_row_start[p + 1] - 1 != t.r0 + tail) ++bad;
-      if (t.cam[l] != 9 * fs.cam_idx[t.r0 + l]) ++bad;
+      if (t.cam[l] != 10 * fs.cam_idx[t.r0 + l]) ++bad;
     }
     for (int l = t.n; l < cb200::kTileObs; ++l)
       if (t.cam[l] != 0 || ((t.seg[l] >> 8) & 255) != l || ((t.seg[l] >> 16) & 255) != l) ++bad;

@@ -23,20 +23,33 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     ap.add_argument("--precond", type=int, default=2)
+    ap.add_argument("--nrep", type=int, nargs="+", default=[0])
+    ap.add_argument("--pcg", type=int, default=0, help="time a solve with exactly this many PCG iterations")
+    ap.add_argument("--period", type=int, default=0)
     args = ap.parse_args()
     pkg = importlib.import_module("ceres-solver-ceres-solver_b200")
     p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, geometry=False)
     values, b, D = p.random_values(1)
     D = np.abs(D) + 1.0
-    g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=args.precond, max_num_iterations=50)
-    g.upload(values, b, D)
-    g.isc_init()
     N, P, C = p.N, p.P, p.C
     bytes_sx = 192 * N + 4 * N + 4 * P + 72 * P + 144 * C
-    for op in args.op:
-        ms, launches = g.time_op(op, warmup=args.warmup, iters=args.iters)
-        print(f"op {op}: {ms:.4f} ms/launch-group ({launches} launches); "
-              f"vs B_Sx={bytes_sx/1e9:.3f} GB -> {bytes_sx/ms/1e6:.0f} GB/s")
+    for nrep in args.nrep:
+        g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=args.precond, max_num_iterations=50,
+                                               y_replicas=nrep, status_check_period=args.period)
+        g.upload(values, b, D)
+        g.isc_init()
+        for op in args.op:
+            ms, launches = g.time_op(op, warmup=args.warmup, iters=args.iters)
+            print(f"nrep {nrep} op {op}: {ms:.4f} ms/launch-group ({launches} launches); "
+                  f"vs B_Sx={bytes_sx/1e9:.3f} GB -> {bytes_sx/ms/1e6:.0f} GB/s", flush=True)
+        if args.pcg:
+            g.set_iterations(args.pcg, args.pcg)
+            for _ in range(3):
+                sm = g.solve_resident(-1.0, -1.0)
+            print(f"pcg {sm['num_iterations']} iterations: setup {sm['setup_ms']:.3f} ms, pcg {sm['pcg_ms']:.3f} ms "
+                  f"({sm['pcg_ms'] / sm['num_iterations'] * 1e3:.1f} us/iteration), back {sm['back_substitute_ms']:.3f} ms, "
+                  f"launches {sm['kernel_launches']}", flush=True)
+        g.close()
 
 
 if __name__ == "__main__":
