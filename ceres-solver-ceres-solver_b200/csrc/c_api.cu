@@ -270,6 +270,8 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
   SET_SMEM(kModeSx, false); SET_SMEM(kModePseZ, false); SET_SMEM(kModeRhs, false);
   SET_SMEM(kModeBack, false); SET_SMEM(kModeRhs, true);
 #undef SET_SMEM
+  TRY_CUDA(cudaFuncSetAttribute(camera_block_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes));
+  TRY_CUDA(cudaFuncSetAttribute(camera_block_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kChunkSmemBytes));
 
   {
     // the fused PCG step needs all its CTAs co-resident (grid barrier)

@@ -24,26 +24,79 @@ constexpr int kChunkThreads = 128;
 // One CTA per chunk (<= kChunkObs rows of one camera, listed camera-major in
 // cam_perm); out: the 45 upper-triangle sums of the chunk.
 // ----------------------------------------------------------------------------
+constexpr int kChunkDepth = 3;     // rows in flight per thread (cp.async pipeline)
+constexpr int kChunkSlot = 176;    // bytes per staged row: F (144) + weights (24), 16-byte aligned
+constexpr int kChunkSmemBytes = kChunkDepth * kChunkThreads * kChunkSlot;
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// The rows of a camera are scattered over the point-major Jacobian, so every
+// thread streams its own rows through a private kChunkDepth-deep cp.async ring
+// in shared memory (a thread only ever reads what it copied itself: no CTA
+// barrier in the loop) while it accumulates the 45 upper-triangle products.
 template <bool WEIGHTED>
 __global__ void __launch_bounds__(kChunkThreads)
 camera_block_kernel(const double* __restrict__ F, const double* __restrict__ weights,
                     const int* __restrict__ cam_perm, const int* __restrict__ chunk_begin,
                     double* __restrict__ chunk_partial) {
+  extern __shared__ __align__(16) unsigned char ring[];
   __shared__ double sred[kChunkThreads / 32][45];
   const int begin = chunk_begin[blockIdx.x], end = chunk_begin[blockIdx.x + 1];
+  unsigned char* mine = ring + threadIdx.x * kChunkSlot;
+  auto slot = [&](int d) { return mine + d * (kChunkThreads * kChunkSlot); };
+  auto issue = [&](int i, int d, int r) {  // r = cam_perm[i], loaded by the caller ahead of time
+    if (i < end) {
+      const double* f = F + (size_t)r * 18;
+      unsigned char* dst = slot(d);
+#pragma unroll
+      for (int k = 0; k < 9; ++k) cp_async16(dst + 16 * k, f + 2 * k);
+      if (WEIGHTED) {
+        const double* w = weights + (size_t)r * 3;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) cp_async8(dst + 144 + 8 * k, w + k);
+      }
+    }
+    cp_async_commit();
+  };
   double acc[45];
 #pragma unroll
   for (int k = 0; k < 45; ++k) acc[k] = 0.0;
-  for (int i = begin + threadIdx.x; i < end; i += kChunkThreads) {
-    const int r = cam_perm[i];
-    const double2* f2 = reinterpret_cast<const double2*>(F + (size_t)r * 18);
+  const int first = begin + threadIdx.x;
+#pragma unroll
+  for (int d = 0; d < kChunkDepth; ++d) {
+    const int i = first + d * kChunkThreads;
+    issue(i, d, i < end ? cam_perm[i] : 0);
+  }
+  // row index of the next refill: loaded one iteration before the copy that needs it
+  int r_next = (first + kChunkDepth * kChunkThreads < end) ? cam_perm[first + kChunkDepth * kChunkThreads] : 0;
+  int d = 0;
+  for (int i = first; i < end; i += kChunkThreads) {
+    cp_async_wait<kChunkDepth - 1>();
+    const double2* f2 = reinterpret_cast<const double2*>(slot(d));
     double f[18];
 #pragma unroll
-    for (int k = 0; k < 9; ++k) { const double2 v = __ldg(f2 + k); f[2 * k] = v.x; f[2 * k + 1] = v.y; }
+    for (int k = 0; k < 9; ++k) { const double2 v = f2[k]; f[2 * k] = v.x; f[2 * k + 1] = v.y; }
+    double w00 = 1.0, w01 = 0.0, w11 = 1.0;
+    if (WEIGHTED) {
+      const double* w = reinterpret_cast<const double*>(slot(d) + 144);
+      w00 = w[0]; w01 = w[1]; w11 = w[2];
+    }
+    issue(i + kChunkDepth * kChunkThreads, d, r_next);  // refill the slot just read
+    {
+      const int i2 = i + (kChunkDepth + 1) * kChunkThreads;
+      r_next = (i2 < end) ? cam_perm[i2] : 0;
+    }
+    d = (d + 1 == kChunkDepth) ? 0 : d + 1;
     double g0[9], g1[9];  // W * F
     if (WEIGHTED) {
-      const double w00 = weights[(size_t)r * 3], w01 = weights[(size_t)r * 3 + 1],
-                   w11 = weights[(size_t)r * 3 + 2];
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
         g0[k] = w00 * f[k] + w01 * f[9 + k];
@@ -59,6 +112,7 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
 #pragma unroll
       for (int j = i2; j < 9; ++j) { acc[q] += f[i2] * g0[j] + f[9 + i2] * g1[j]; ++q; }
   }
+  cp_async_wait<0>();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < 45; ++k) {

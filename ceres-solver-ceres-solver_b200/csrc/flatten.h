@@ -22,6 +22,11 @@
 namespace cb200 {
 
 constexpr int kTileObs = 32;  // rows per tile of the fused per-point kernels: one lane each
+constexpr int kChunkedPointRows = 256;  // points of 33..256 rows run as chunk tiles inside the stream kernel
+// flags in TileMeta::np above the point count (low 8 bits)
+constexpr int kTileKindShift = 8;        // bits 8-9: 0 whole points, 1 first-pass chunk, 2 second-pass chunk
+constexpr int kTileLastChunk = 1 << 10;  // last first-pass chunk of its point: the point's sums are complete
+constexpr int kTileContinues = 1 << 11;  // not the first tile of its group: warp ranges may not start here
 
 struct FlatStructure {
   int num_points = 0;      // P: eliminated (E) column blocks, size 3
@@ -118,8 +123,11 @@ inline std::vector<int> ShardPoints(const std::vector<int>& point_row_start, int
 
 // Tile plan of the fused per-point kernels: a tile is the unit of work of ONE
 // WARP: whole points [p0, p0 + np) whose rows [r0, r0 + n) fit the 32 lanes.
-// Points with more rows than a tile go to long_points (CTA-per-point kernel),
-// points without rows to empty_points. Indices are LOCAL to the shard (point 0
+// A point of 33..kChunkedPointRows rows becomes a group of chunk tiles that one
+// warp runs back to back: first-pass chunks accumulate the point's sums, then
+// second-pass chunks (the same rows again, now L2 hits) apply the result.
+// Longer points go to long_points (CTA-per-point kernel), points without rows
+// to empty_points. Indices are LOCAL to the shard (point 0
 // = first point of the shard). One TileMeta record per tile is the static
 // side-band the device streams next to the Jacobian blocks (one bulk copy).
 struct alignas(16) TileMeta {
@@ -161,12 +169,33 @@ inline TilePlan PlanTiles(const int* row_start /* local, P_loc+1 */, const int* 
     members.clear();
     open_rows = 0;
   };
+  auto emit_chunks = [&](int p) {
+    const int r0 = row_start[p], len = row_start[p + 1] - r0;
+    const int chunks = (len + kTileObs - 1) / kTileObs;
+    for (int pass = 1; pass <= 2; ++pass)
+      for (int ch = 0; ch < chunks; ++ch) {
+        TileMeta m;
+        std::memset(&m, 0, sizeof(m));
+        m.r0 = r0 + ch * kTileObs;
+        m.n = std::min(kTileObs, len - ch * kTileObs);
+        m.p0 = p;
+        m.np = 1 | (pass << kTileKindShift) | ((pass == 1 && ch == chunks - 1) ? kTileLastChunk : 0) |
+               ((pass == 1 && ch == 0) ? 0 : kTileContinues);
+        for (int l = 0; l < kTileObs; ++l) m.seg[l] = 0 | (l << 8) | (l << 16);
+        for (int l = 0; l < m.n; ++l) {
+          m.cam[l] = 10 * cam[m.r0 + l];
+          m.seg[l] = 0 | (0 << 8) | ((m.n - 1) << 16);
+        }
+        plan.tiles.push_back(m);
+      }
+  };
   for (int p = 0; p < P_loc; ++p) {
     const int len = row_start[p + 1] - row_start[p];
     if (len == 0) { plan.empty_points.push_back(p); continue; }  // (rows stay contiguous)
     if (len > kTileObs) {
       emit();
-      plan.long_points.push_back(p);
+      if (len <= kChunkedPointRows) emit_chunks(p);
+      else plan.long_points.push_back(p);
       continue;
     }
     if (open_rows + len > kTileObs) emit();

@@ -74,7 +74,8 @@ struct StreamLayout {
   // per warp: stages, then the 32 x 10 transposition scratch, then the barriers
   static constexpr int kOffX = kStages * kStageBytes;
   static constexpr int kOffBars = kOffX + 320 * 8;
-  static constexpr int kWarpBytes = kOffBars + 16 * ((kStages * 8 + 15) / 16);
+  static constexpr int kOffCarry = kOffBars + 16 * ((kStages * 8 + 15) / 16);  // 18 doubles, long points only
+  static constexpr int kWarpBytes = kOffCarry + 144;
   static constexpr int kSmemBytes = kStreamWarps * kWarpBytes;
 };
 
@@ -83,13 +84,13 @@ __device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, const int4
                                           unsigned char* st, uint64_t* bar, uint64_t stream_policy) {
   const bool use_b = L::kUsesB && a.b != nullptr;
   const uint32_t bytes = (uint32_t)h.y * 192u + (uint32_t)kMetaBytes +
-                         (L::kLoadsInv ? (uint32_t)h.w * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
+                         (L::kLoadsInv ? (uint32_t)(h.w & 255) * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
   mbar_expect_tx(bar, bytes);
   bulk_g2s(st + L::kOffMeta, a.tiles + t, (uint32_t)kMetaBytes, bar);
   // Jacobian blocks and b are read once per pass: first in line for eviction
   bulk_g2s_hint(st + L::kOffE, a.E + (size_t)h.x * 6, (uint32_t)h.y * 48u, bar, stream_policy);
   bulk_g2s_hint(st + L::kOffF, a.F + (size_t)h.x * 18, (uint32_t)h.y * 144u, bar, stream_policy);
-  if (L::kLoadsInv) bulk_g2s(st + L::kOffInv, a.ete_inv + (size_t)h.z * 6, (uint32_t)h.w * 48u, bar);
+  if (L::kLoadsInv) bulk_g2s(st + L::kOffInv, a.ete_inv + (size_t)h.z * 6, (uint32_t)(h.w & 255) * 48u, bar);
   if (use_b) bulk_g2s_hint(st + L::kOffB, a.b + (size_t)h.x * 2, (uint32_t)h.y * 16u, bar, stream_policy);
 }
 
@@ -135,8 +136,11 @@ point_stream_kernel(const StreamArgs a) {
   // contiguous tile range of this warp
   const int gw = blockIdx.x * kStreamWarps + warp;
   const int GW = gridDim.x * kStreamWarps;
-  const int t_begin = (int)((long long)a.num_tiles * gw / GW);
-  const int t_end = (int)((long long)a.num_tiles * (gw + 1) / GW);
+  int t_begin = (int)((long long)a.num_tiles * gw / GW);
+  int t_end = (int)((long long)a.num_tiles * (gw + 1) / GW);
+  // a group of chunk tiles (one long point) stays with one warp: ranges start at group starts
+  while (t_begin < a.num_tiles && (LoadHeader(a.tiles + t_begin).w & kTileContinues)) ++t_begin;
+  while (t_end < a.num_tiles && (LoadHeader(a.tiles + t_end).w & kTileContinues)) ++t_end;
   if (t_begin >= t_end) return;
   // header of the tile to issue next, loaded one iteration before it is needed
   int4 hnext = make_int4(0, 0, 0, 0);
@@ -172,12 +176,23 @@ point_stream_kernel(const StreamArgs a) {
     gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMeta));
   }
 
+  // carry of a long point across its chunk tiles: kept in shared memory (touched by chunk
+  // tiles only, so it costs the common path no registers); every lane reads / writes the same
+  double* cu = reinterpret_cast<double*>(wsm + L::kOffCarry);  // [3] running sums of u
+  double* cv = cu + 3;                                          // [3] v of the finished point
+  double* cq = cu + 6;                                          // [6] running sums of E'E
+  double* cc = cu + 12;                                         // [6] adjugate inverse of the finished point
+  if (lane < 18) cu[lane] = 0.0;
+  __syncwarp();
+
   for (int t = t_begin, i = 0; t < t_end; ++t, ++i) {
     const int s = i % L::kStages;
     unsigned char* st = wsm + s * L::kStageBytes;
     mbar_wait(full + s, (i / L::kStages) & 1);
     const TileMeta* m = reinterpret_cast<const TileMeta*>(st + L::kOffMeta);
     const int r0 = m->r0, n = m->n, p0 = m->p0;
+    const int flags = m->np;
+    const int kind = (flags >> kTileKindShift) & 3;  // 0 whole points, 1 / 2 chunk of a long point
     // ---- everything this lane needs from the stage goes to registers ----
     double Ei[6], Fi[18];
     double t0 = 0.0, t1 = 0.0;
@@ -255,33 +270,54 @@ point_stream_kernel(const StreamArgs a) {
     double u1 = SegScan(Ei[1] * t0 + Ei[4] * t1, km);
     double u2 = SegScan(Ei[2] * t0 + Ei[5] * t1, km);
     double c6[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};  // adjugate inverse (Schur-Jacobi weights)
+    double q[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     if (BUILD) {
-      double q[6];
       q[0] = SegScan(Ei[0] * Ei[0] + Ei[3] * Ei[3], km);
       q[1] = SegScan(Ei[0] * Ei[1] + Ei[3] * Ei[4], km);
       q[2] = SegScan(Ei[0] * Ei[2] + Ei[3] * Ei[5], km);
       q[3] = SegScan(Ei[1] * Ei[1] + Ei[4] * Ei[4], km);
       q[4] = SegScan(Ei[1] * Ei[2] + Ei[4] * Ei[5], km);
       q[5] = SegScan(Ei[2] * Ei[2] + Ei[5] * Ei[5], km);
-      if (is_tail) {
-        double mm[9] = {q[0], q[1], q[2], q[1], q[3], q[4], q[2], q[4], q[5]};
-        mm[0] += de0 * de0; mm[4] += de1 * de1; mm[8] += de2 * de2;
-        if (a.weights != nullptr) {
-          double c[9];
-          Inverse3x3(mm, c);
-          c6[0] = c[0]; c6[1] = c[1]; c6[2] = c[2]; c6[3] = c[4]; c6[4] = c[5]; c6[5] = c[8];
-        }
-        LltInverseUpper<3>(mm);
-        inv[0] = mm[0]; inv[1] = mm[1]; inv[2] = mm[2]; inv[3] = mm[4]; inv[4] = mm[5]; inv[5] = mm[8];
-        double2* g = reinterpret_cast<double2*>(a.ete_inv + (size_t)(p0 + pt) * 6);
-        g[0] = make_double2(inv[0], inv[1]);
-        g[1] = make_double2(inv[2], inv[3]);
-        g[2] = make_double2(inv[4], inv[5]);
+    }
+    if (kind == 1) {
+      // first-pass chunk of a long point: add the chunk's sums (at lane n-1) to the carry
+      u0 = cu[0] + __shfl_sync(0xffffffffu, u0, n - 1);
+      u1 = cu[1] + __shfl_sync(0xffffffffu, u1, n - 1);
+      u2 = cu[2] + __shfl_sync(0xffffffffu, u2, n - 1);
+      if (BUILD) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) q[k] = cq[k] + __shfl_sync(0xffffffffu, q[k], n - 1);
       }
+      const bool last = (flags & kTileLastChunk) != 0;
+      __syncwarp();
+      if (lane == 0) {
+        cu[0] = last ? 0.0 : u0; cu[1] = last ? 0.0 : u1; cu[2] = last ? 0.0 : u2;
+        if (BUILD) {
+#pragma unroll
+          for (int k = 0; k < 6; ++k) cq[k] = last ? 0.0 : q[k];
+        }
+      }
+      __syncwarp();
+      if (!last) continue;
+    }
+    if (BUILD && is_tail && kind != 2) {
+      double mm[9] = {q[0], q[1], q[2], q[1], q[3], q[4], q[2], q[4], q[5]};
+      mm[0] += de0 * de0; mm[4] += de1 * de1; mm[8] += de2 * de2;
+      if (a.weights != nullptr) {
+        double c[9];
+        Inverse3x3(mm, c);
+        c6[0] = c[0]; c6[1] = c[1]; c6[2] = c[2]; c6[3] = c[4]; c6[4] = c[5]; c6[5] = c[8];
+      }
+      LltInverseUpper<3>(mm);
+      inv[0] = mm[0]; inv[1] = mm[1]; inv[2] = mm[2]; inv[3] = mm[4]; inv[4] = mm[5]; inv[5] = mm[8];
+      double2* g = reinterpret_cast<double2*>(a.ete_inv + (size_t)(p0 + pt) * 6);
+      g[0] = make_double2(inv[0], inv[1]);
+      g[1] = make_double2(inv[2], inv[3]);
+      g[2] = make_double2(inv[4], inv[5]);
     }
     // ---- v = inverse * u at the point's last row, then to all its rows ----
     double v0 = 0.0, v1 = 0.0, v2 = 0.0;
-    if (is_tail) {
+    if (is_tail && kind != 2) {
       v0 = inv[0] * u0 + inv[1] * u1 + inv[2] * u2;
       v1 = inv[1] * u0 + inv[3] * u1 + inv[4] * u2;
       v2 = inv[2] * u0 + inv[4] * u1 + inv[5] * u2;
@@ -291,9 +327,30 @@ point_stream_kernel(const StreamArgs a) {
       }
     }
     if (MODE == kModeBack) continue;
-    v0 = __shfl_sync(0xffffffffu, v0, tail);
-    v1 = __shfl_sync(0xffffffffu, v1, tail);
-    v2 = __shfl_sync(0xffffffffu, v2, tail);
+    // (a chunk's carry must be the same in every lane, idle ones included: they are live rows later)
+    const int src = (kind == 1) ? n - 1 : tail;
+    v0 = __shfl_sync(0xffffffffu, v0, src);
+    v1 = __shfl_sync(0xffffffffu, v1, src);
+    v2 = __shfl_sync(0xffffffffu, v2, src);
+    if (BUILD && a.weights != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) c6[k] = __shfl_sync(0xffffffffu, c6[k], src);
+    }
+    if (kind == 1) {
+      // the point's sums are complete: keep v (and the adjugate inverse) for its second-pass chunks
+      if (lane == 0) {
+        cv[0] = v0; cv[1] = v1; cv[2] = v2;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) cc[k] = c6[k];
+      }
+      __syncwarp();
+      continue;
+    }
+    if (kind == 2) {
+      v0 = cv[0]; v1 = cv[1]; v2 = cv[2];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) c6[k] = cc[k];
+    }
     // ---- w_r = t_r - E_r v (or E_r v); F_r' w_r goes to the camera accumulator ----
     {
       const double ev0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2;
@@ -305,8 +362,6 @@ point_stream_kernel(const StreamArgs a) {
     }
     if (BUILD && a.weights != nullptr) {
       // W_r = I - E_r c E_r' with c the adjugate inverse (InvertPSDMatrix<3>)
-#pragma unroll
-      for (int k = 0; k < 6; ++k) c6[k] = __shfl_sync(0xffffffffu, c6[k], tail);
       const double g00 = Ei[0] * c6[0] + Ei[1] * c6[1] + Ei[2] * c6[2];
       const double g01 = Ei[0] * c6[1] + Ei[1] * c6[3] + Ei[2] * c6[4];
       const double g02 = Ei[0] * c6[2] + Ei[1] * c6[4] + Ei[2] * c6[5];

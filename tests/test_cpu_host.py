@@ -98,7 +98,10 @@ def test_adapter_header_flattens_a_ceres_block_structure(tmp_path):
     kv = dict(t.split("=") for t in out.split())
     assert kv["flatten"] == "0" and kv["canonical"] == "1" and kv["bad"] == "0", out
     N = int(kv["N"])
-    assert int(kv["rows_in_tiles"]) == N - 45 and kv["long"] == "1" and kv["empty"] == "1", out
+    assert int(kv["rows_in_tiles"]) == N - 45 - 300 and kv["long"] == "1" and kv["empty"] == "1", out
+    # the 45-row point: two first-pass chunks and two second-pass chunks in one group
+    assert kv["chunk1"] == "45" and kv["chunk2"] == "45", out
+    assert int(kv["groups"]) == int(kv["tiles"]) - 3, out
     sh = [int(t) for t in kv["shard"].split(",")]
     assert sh[0] == 0 and sh[3] == 40 and sh[0] <= sh[1] <= sh[2] <= sh[3], out
     assert kv["create"] == ("0" if util.has_gpu() else "-3"), out

@@ -163,11 +163,16 @@ def test_duplicate_and_long_points():
     # duplicates of a (point, camera) pair: schur_eliminator_impl.h:140-148
     _, p, values, b, D = small_problem(C=9, P=200, N=900, seed=8, dup_pairs=40)
     compare_solve(m, p.structure, values, b, D, "SCHUR_JACOBI")
-    # a point seen by 300 cameras does not fit one CTA tile
+    # points of 33..256 rows run as chunk tiles of the stream kernel, longer ones in the
+    # CTA-per-point kernel
     C, P = 300, 40
     lens = np.full(P, 3)
     lens[7] = 300
     lens[20] = 257
+    lens[12] = 100
+    lens[30] = 33
+    lens[31] = 64
+    lens[39] = 256
     prs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
     rng = np.random.default_rng(0)
     cam = np.concatenate([np.sort(rng.choice(C, size=L, replace=False)) for L in lens]).astype(np.int32)
