@@ -100,7 +100,7 @@ def run_reference(args, rank):
     cores = os.cpu_count()
     ost = ob.Structure(st.row_size, st.row_pos, st.cell_ptr, st.cell_block_id, st.cell_position, st.col_size,
                        st.col_pos, st.num_eliminate_blocks)
-    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=MAX_PCG,
+    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=PRECOND[args.precond], max_num_iterations=MAX_PCG,
                   native=True)
     # bounded sample: at ~1 s per solve on 16 cores the driver's K steps are capped so the run ends in
     # about a minute; every timed step is a full solve of the same problem
@@ -126,9 +126,14 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+PRECOND = {"identity": 0, "jacobi": 1, "schur_jacobi": 2, "spse": 3}
+PRECOND_NAME = {"identity": "IDENTITY", "jacobi": "JACOBI", "schur_jacobi": "SCHUR_JACOBI",
+                "spse": "SCHUR_POWER_SERIES_EXPANSION"}
+
+
 def workload_config(args, p):
     return {"workload": f"synthetic BAL {args.shape}-shape x{args.scale:g}: {p.C} cameras, {p.P} points, "
-                        f"{p.N} observations; ITERATIVE_SCHUR + SCHUR_JACOBI, eta={ETA}, first LM iteration "
+                        f"{p.N} observations; ITERATIVE_SCHUR + {PRECOND_NAME[args.precond]}, eta={ETA}, first LM iteration "
                         f"(Jacobi-scaled Snavely Jacobian, radius {RADIUS:g})",
             "cameras": p.C, "points": p.P, "observations": p.N,
             "l2": "inputs (24*N doubles) exceed the 126 MB L2; no flush needed"}
@@ -143,6 +148,7 @@ def main():
     ap.add_argument("--shape", default="venice")
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precond", default="schur_jacobi", choices=["schur_jacobi", "spse", "jacobi", "identity"])
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -173,7 +179,7 @@ def main():
 
     hv, hb, hD = pinned(values), pinned(residuals), pinned(D)
     hx = torch.zeros(3 * p.P + 9 * p.C, dtype=torch.float64, pin_memory=True)
-    g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=pkg.SCHUR_JACOBI,
+    g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=PRECOND[args.precond],
                                            max_num_iterations=MAX_PCG, device_id=local_rank, rank=rank,
                                            world_size=world, nccl_unique_id=uid)
 
@@ -237,9 +243,16 @@ def main():
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None  # dram__bytes_read + dram__bytes_write of one launch, from the committed ncu capture
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r1_sx_traffic.json")))
+        if world == 1 and args.shape == t.get("shape") and args.scale == 1.0:
+            traffic = t["traffic_bytes_per_launch"]
+    except Exception:
+        pass
     achieved = bytes_sx / (sx_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "point_stream_kernel<kModeSx> (+ point_long_kernel for points of > 32 rows)", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    roofline = {"bound": "hbm", "kernel": "point_stream_kernel<kModeSx> (+ point_long_kernel for points of > 256 rows)", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
                 "bytes_per_launch": bytes_sx, "ms_per_launch": sx_ms}
 
@@ -256,7 +269,7 @@ def main():
                         "wall_ms_per_step": e2e_wall_ms / args.steps, "h2d_ms": s2["h2d_ms"], "d2h_ms": s2["d2h_ms"]},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline}
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(p, values, residuals, D)
+            line["cpu_baseline"] = cpu_baseline(p, values, residuals, D, PRECOND[args.precond])
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -264,14 +277,14 @@ def main():
         dist.destroy_process_group()
 
 
-def cpu_baseline(p, values, residuals, D):
+def cpu_baseline(p, values, residuals, D, precond):
     """Oracle port of the reference's CPU path, all host threads, one full solve of the same problem."""
     from oracle import binding as ob
     st = p.structure
     cores = os.cpu_count()
     ost = ob.Structure(st.row_size, st.row_pos, st.cell_ptr, st.cell_block_id, st.cell_position, st.col_size,
                        st.col_pos, st.num_eliminate_blocks)
-    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=MAX_PCG, native=True)
+    o = ob.Oracle(ost, num_threads=cores, preconditioner_type=precond, max_num_iterations=MAX_PCG, native=True)
     t0 = time.perf_counter()
     _, s = o.solve(values, residuals, D, ETA, -1.0)
     dt = time.perf_counter() - t0
