@@ -13,7 +13,7 @@ LIB_CUDA = os.path.join(HERE, "libceres_b200_schur.so")
 LIB_BAL = os.path.join(HERE, "libsynthetic_bal.so")
 LIB_LM = os.path.join(HERE, "libceres_b200_lm.so")
 
-_CUDA_SRC = ["c_api.cu", "c_api_solve.inc", "c_api_entry.inc", "kernels.cuh", "camera_kernels.cuh",
+_CUDA_SRC = ["c_api.cu", "c_api_solve.inc", "c_api_entry.inc", "c_api_lm.inc", "lm_kernels.cuh", "snavely_model.h", "kernels.cuh", "camera_kernels.cuh",
              "cg_kernels.cuh", "cg_step.cuh", "stream_kernels.cuh", "solver_state.h", "flatten.h"]
 
 
@@ -45,7 +45,7 @@ def build_cuda(force=False, verbose=False):
 
 def build_bal(force=False):
     src = os.path.join(CSRC, "synthetic_bal.cc")
-    if not force and not _stale(LIB_BAL, [src]):
+    if not force and not _stale(LIB_BAL, [src, os.path.join(CSRC, "snavely_model.h")]):
         return LIB_BAL
     # x86-64-v3 (not -march=native): the .so is built here and run on the GPU box
     subprocess.run(["g++", "-O3", "-march=x86-64-v3", "-std=c++17", "-fopenmp", "-fPIC", "-shared",

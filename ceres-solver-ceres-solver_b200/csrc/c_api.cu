@@ -5,6 +5,8 @@
 #include <dlfcn.h>
 
 #include <algorithm>
+#include <chrono>
+#include <limits>
 #include <cmath>
 #include <cstddef>
 #include <cstdio>
@@ -16,6 +18,7 @@
 #include "cg_kernels.cuh"
 #include "cg_step.cuh"
 #include "kernels.cuh"
+#include "lm_kernels.cuh"
 #include "solver_state.h"
 #include "stream_kernels.cuh"
 
@@ -115,6 +118,7 @@ void cb200_destroy(cb200_solver* s) {
   if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
   for (void* p : s->allocations) cudaFree(p);
   if (s->h_cg) cudaFreeHost(s->h_cg);
+  if (s->h_lm_scalars) cudaFreeHost(s->h_lm_scalars);
   for (auto& e : s->ev)
     if (e) cudaEventDestroy(e);
   if (s->stream) cudaStreamDestroy(s->stream);
@@ -332,3 +336,4 @@ int cb200_shard(const cb200_solver* s, int* pb, int* pe, int* rb, int* re) {
 
 #include "c_api_solve.inc"
 #include "c_api_entry.inc"
+#include "c_api_lm.inc"

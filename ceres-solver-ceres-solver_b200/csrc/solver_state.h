@@ -60,6 +60,7 @@ struct cb200_solver {
   double *d_ete_inv = nullptr, *d_weights = nullptr, *d_chunk_partial = nullptr, *d_upper = nullptr;
   double *d_dup_blocks = nullptr, *d_sj = nullptr, *d_ftf_inv = nullptr;
   double *d_yrep = nullptr, *d_y_e = nullptr, *d_ete9 = nullptr;
+  double* d_model = nullptr;  // when set, back substitution also accumulates the model cost change here
   double* d_x10 = nullptr;  // the vector being multiplied, padded to 10 doubles per camera (16-byte gathers)
   // device: camera vectors
   double *d_rhs = nullptr, *d_x = nullptr, *d_r = nullptr, *d_p = nullptr, *d_z = nullptr, *d_q = nullptr;
@@ -69,6 +70,19 @@ struct cb200_solver {
   double* d_trace = nullptr;
   double* h_trace = nullptr;
   int max_trace = 0;
+
+  // widened boundary: device-resident bundle adjustment problem (c_api_lm.inc)
+  bool bal_attached = false, bal_params = false;
+  double *d_obs = nullptr, *d_cameras = nullptr, *d_points = nullptr, *d_cand_cameras = nullptr,
+         *d_cand_points = nullptr;
+  int* d_row_point = nullptr;
+  double *d_scale = nullptr;       // [3 P_loc + 9C] Jacobi scaling (points, then cameras)
+  double *d_norm2 = nullptr;       // [3 P_loc + 9C] squared column norms of the unscaled Jacobian
+  double *d_grad = nullptr;        // [3 P_loc + 9C] J'r
+  double *d_cost_partial = nullptr;
+  double *d_lm_scalars = nullptr;  // cost, model, |x|^2, |delta|^2, gradient max, gradient norm^2
+  double *h_lm_scalars = nullptr;  // pinned
+  int eval_blocks = 0;
 
   cb200::Nccl nccl;
   int launches = 0;

@@ -57,6 +57,8 @@ struct StreamArgs {
   int rep_stride;
   double* y_e;              // [3P] (kModeBack)
   const int* done;          // device convergence flag; the kernel is a no-op when set
+  double* model;            // (kModeBack) or null: accumulates sum_rows m.(b - m/2) with m = E y_e + F x, the
+                            // model cost change of the step -y (trust_region_minimizer.cc:430-438)
 };
 
 template <int MODE, bool BUILD>
@@ -196,6 +198,7 @@ point_stream_kernel(const StreamArgs a) {
     // ---- everything this lane needs from the stage goes to registers ----
     double Ei[6], Fi[18];
     double t0 = 0.0, t1 = 0.0;
+    double fz0 = 0.0, fz1 = 0.0;  // (kModeBack) F x of this row
     const int cam = m->cam[lane];
     const int seg = m->seg[lane];
     const int pt = seg & 255, head = (seg >> 8) & 255, tail = (seg >> 16) & 255;
@@ -261,7 +264,7 @@ point_stream_kernel(const StreamArgs a) {
       }
       f0 = fma(Fi[8], xr[8], f0) + f0b;
       f1 = fma(Fi[17], xr[8], f1) + f1b;
-      if (MODE == kModeBack) { t0 -= f0; t1 -= f1; } else { t0 = f0; t1 = f1; }
+      if (MODE == kModeBack) { t0 -= f0; t1 -= f1; fz0 = f0; fz1 = f1; } else { t0 = f0; t1 = f1; }
       __syncwarp();  // sXw is reused by the scatter below
     }
     // ---- u = sum over the point's rows of E_r' t_r (and of E_r'E_r) ----
@@ -326,7 +329,7 @@ point_stream_kernel(const StreamArgs a) {
         y[0] = v0; y[1] = v1; y[2] = v2;
       }
     }
-    if (MODE == kModeBack) continue;
+    if (MODE == kModeBack && a.model == nullptr) continue;
     // (a chunk's carry must be the same in every lane, idle ones included: they are live rows later)
     const int src = (kind == 1) ? n - 1 : tail;
     v0 = __shfl_sync(0xffffffffu, v0, src);
@@ -350,6 +353,16 @@ point_stream_kernel(const StreamArgs a) {
       v0 = cv[0]; v1 = cv[1]; v2 = cv[2];
 #pragma unroll
       for (int k = 0; k < 6; ++k) c6[k] = cc[k];
+    }
+    if (MODE == kModeBack) {
+      // model cost change of the step -y: m = J y for this row, b = t + F x
+      const double m0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2 + fz0;
+      const double m1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2 + fz1;
+      double val = active ? m0 * (t0 + fz0 - 0.5 * m0) + m1 * (t1 + fz1 - 0.5 * m1) : 0.0;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
+      if (lane == 0) atomicAdd(a.model, val);
+      continue;
     }
     // ---- w_r = t_r - E_r v (or E_r v); F_r' w_r goes to the camera accumulator ----
     {
@@ -465,6 +478,19 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
   const double v2 = inv[2] * u[0] + inv[4] * u[1] + inv[5] * u[2];
   if (MODE == kModeBack) {
     if (threadIdx.x == 0) { a.y_e[3 * (size_t)p] = v0; a.y_e[3 * (size_t)p + 1] = v1; a.y_e[3 * (size_t)p + 2] = v2; }
+    if (a.model != nullptr) {
+      double val = 0.0;
+      for (int r = r0 + threadIdx.x; r < r1; r += blockDim.x) {
+        const double* Ei = a.E + (size_t)r * 6;
+        const double* Fi = a.F + (size_t)r * 18;
+        const double* x = a.x + 10 * (size_t)cam[r];
+        double m0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2, m1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
+        for (int k = 0; k < 9; ++k) { m0 += Fi[k] * x[k]; m1 += Fi[9 + k] * x[k]; }
+        val += m0 * (a.b[2 * (size_t)r] - 0.5 * m0) + m1 * (a.b[2 * (size_t)r + 1] - 0.5 * m1);
+      }
+      val = BlockSum(val, sbuf);
+      if (threadIdx.x == 0) atomicAdd(a.model, val);
+    }
     return;
   }
   double* y = a.yrep + (size_t)(blockIdx.x % a.nrep) * a.rep_stride;

@@ -44,6 +44,39 @@ class CSummary(ctypes.Structure):
                 ("kernel_launches", ctypes.c_int)]
 
 
+class CLmOptions(ctypes.Structure):
+    _fields_ = [("max_num_iterations", ctypes.c_int), ("initial_trust_region_radius", ctypes.c_double),
+                ("max_trust_region_radius", ctypes.c_double), ("min_trust_region_radius", ctypes.c_double),
+                ("min_relative_decrease", ctypes.c_double), ("min_lm_diagonal", ctypes.c_double),
+                ("max_lm_diagonal", ctypes.c_double), ("eta", ctypes.c_double),
+                ("function_tolerance", ctypes.c_double), ("gradient_tolerance", ctypes.c_double),
+                ("parameter_tolerance", ctypes.c_double), ("jacobi_scaling", ctypes.c_int),
+                ("max_num_consecutive_invalid_steps", ctypes.c_int)]
+
+
+class CLmIteration(ctypes.Structure):
+    _fields_ = [("iteration", ctypes.c_int), ("step_is_valid", ctypes.c_int), ("step_is_successful", ctypes.c_int),
+                ("cost", ctypes.c_double), ("cost_change", ctypes.c_double), ("gradient_max_norm", ctypes.c_double),
+                ("gradient_norm", ctypes.c_double), ("step_norm", ctypes.c_double),
+                ("relative_decrease", ctypes.c_double), ("trust_region_radius", ctypes.c_double),
+                ("eta", ctypes.c_double), ("linear_solver_iterations", ctypes.c_int),
+                ("iteration_ms", ctypes.c_float)]
+
+
+class CLmSummary(ctypes.Structure):
+    _fields_ = [("initial_cost", ctypes.c_double), ("final_cost", ctypes.c_double), ("num_iterations", ctypes.c_int),
+                ("num_successful_steps", ctypes.c_int), ("num_unsuccessful_steps", ctypes.c_int),
+                ("termination_type", ctypes.c_int), ("message", ctypes.c_char * 256),
+                ("total_ms", ctypes.c_float), ("evaluate_ms", ctypes.c_float), ("linear_solver_ms", ctypes.c_float),
+                ("num_linear_solver_iterations", ctypes.c_int)]
+
+
+LM_DEFAULTS = dict(max_num_iterations=50, initial_trust_region_radius=1e4, max_trust_region_radius=1e16,
+                   min_trust_region_radius=1e-32, min_relative_decrease=1e-3, min_lm_diagonal=1e-6,
+                   max_lm_diagonal=1e32, eta=1e-1, function_tolerance=1e-6, gradient_tolerance=1e-10,
+                   parameter_tolerance=1e-8, jacobi_scaling=1, max_num_consecutive_invalid_steps=5)
+LM_TERMINATION = {0: "CONVERGENCE", 1: "NO_CONVERGENCE", 2: "FAILURE"}
+
 # every symbol include/ceres_b200_schur.h declares: name -> (restype, argtypes)
 _H = ctypes.c_void_p
 SYMBOLS = {
@@ -84,6 +117,13 @@ SYMBOLS = {
     "cb200_pse_apply": (ctypes.c_int, [_H, ctypes.c_int, ctypes.c_double, _dp, _dp]),
     "cb200_time_op": (ctypes.c_int, [_H, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                      ctypes.POINTER(ctypes.c_float), _ip]),
+    "cb200_bal_attach": (ctypes.c_int, [_H, _dp]),
+    "cb200_bal_set_parameters": (ctypes.c_int, [_H, _dp, _dp]),
+    "cb200_bal_get_parameters": (ctypes.c_int, [_H, _dp, _dp]),
+    "cb200_bal_evaluate": (ctypes.c_int, [_H, ctypes.c_int, _dp, _dp]),
+    "cb200_download_jacobian": (ctypes.c_int, [_H, _dp, _dp]),
+    "cb200_lm_minimize": (ctypes.c_int, [_H, ctypes.POINTER(CLmOptions), ctypes.POINTER(CLmSummary),
+                                         ctypes.POINTER(CLmIteration), ctypes.c_int]),
 }
 
 _LIB = None
@@ -327,6 +367,47 @@ class IterativeSchurComplementSolver:
         y = np.zeros(self.num_cols_f)
         _check(self.L.cb200_pse_apply(self.h, max_num_spse_iterations, spse_tolerance, _d(x), _d(y)))
         return y
+
+    # --- widened boundary: device evaluator + trust-region loop -------------
+    def bal_attach(self, observations):
+        _check(self.L.cb200_bal_attach(self.h, _d(np.ascontiguousarray(observations, dtype=np.float64))))
+
+    def bal_set_parameters(self, cameras, points):
+        _check(self.L.cb200_bal_set_parameters(self.h, _d(np.ascontiguousarray(cameras, dtype=np.float64)),
+                                               _d(np.ascontiguousarray(points, dtype=np.float64))))
+
+    def bal_get_parameters(self):
+        cameras = np.zeros(self.num_cols_f)
+        points = np.full(self.num_cols - self.num_cols_f, np.nan)
+        _check(self.L.cb200_bal_get_parameters(self.h, _d(cameras), _d(points)))
+        return cameras, points
+
+    def bal_evaluate(self, jacobian=True):
+        cost = ctypes.c_double()
+        gradient = np.full(self.num_cols, np.nan) if jacobian else None
+        _check(self.L.cb200_bal_evaluate(self.h, int(jacobian), ctypes.byref(cost), _d(gradient)))
+        return cost.value, gradient
+
+    def download_jacobian(self):
+        values = np.full(12 * self.num_rows, np.nan)
+        residuals = np.full(self.num_rows, np.nan)
+        _check(self.L.cb200_download_jacobian(self.h, _d(values), _d(residuals)))
+        return values, residuals
+
+    def lm_minimize(self, **options):
+        o = dict(LM_DEFAULTS)
+        o.update(options)
+        co = CLmOptions(**o)
+        cap = o["max_num_iterations"] + 2
+        its = (CLmIteration * cap)()
+        cs = CLmSummary()
+        _check(self.L.cb200_lm_minimize(self.h, ctypes.byref(co), ctypes.byref(cs), its, cap))
+        out = {k: getattr(cs, k) for k, _ in CLmSummary._fields_}
+        out["message"] = cs.message.decode()
+        out["termination_type"] = LM_TERMINATION[cs.termination_type]
+        out["iterations"] = [{k: getattr(its[i], k) for k, _ in CLmIteration._fields_}
+                             for i in range(cs.num_iterations)]
+        return out
 
     def time_op(self, op, warmup=3, iters=10):
         ms, n = ctypes.c_float(), ctypes.c_int()

@@ -211,6 +211,72 @@ int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
 int cb200_time_op(cb200_solver* s, int op, int warmup, int iters, float* ms_out,
                   int* launches_out);
 
+/* ---- widened boundary: the Snavely bundle-adjustment
+ * evaluator and the trust-region loop run on the device-resident problem, so the
+ * Jacobian never crosses PCIe. The structure given to cb200_create must be the
+ * evaluator's canonical layout. -------------------------------------------------- */
+
+/* ceres::TerminationType (include/ceres/types.h) */
+enum { CB200_CONVERGENCE = 0, CB200_NO_CONVERGENCE = 1, CB200_FAILURE = 2 };
+
+/* The Solver::Options fields TrustRegionMinimizer and LevenbergMarquardtStrategy
+ * consume (include/ceres/solver.h:263-321, trust_region_minimizer.cc,
+ * levenberg_marquardt_strategy.cc:46-65). */
+typedef struct cb200_lm_options {
+  int max_num_iterations;               /* 50                                   */
+  double initial_trust_region_radius;   /* 1e4                                  */
+  double max_trust_region_radius;       /* 1e16                                 */
+  double min_trust_region_radius;       /* 1e-32                                */
+  double min_relative_decrease;         /* 1e-3                                 */
+  double min_lm_diagonal;               /* 1e-6                                 */
+  double max_lm_diagonal;               /* 1e32                                 */
+  double eta;                           /* 1e-1 (bundle_adjuster.cc:114: 1e-2)  */
+  double function_tolerance;            /* 1e-6                                 */
+  double gradient_tolerance;            /* 1e-10                                */
+  double parameter_tolerance;           /* 1e-8                                 */
+  int jacobi_scaling;                   /* 1                                    */
+  int max_num_consecutive_invalid_steps;/* 5                                    */
+} cb200_lm_options;
+
+/* ceres::IterationSummary (include/ceres/iteration_callback.h), the fields this loop fills */
+typedef struct cb200_lm_iteration {
+  int iteration;
+  int step_is_valid, step_is_successful;
+  double cost, cost_change, gradient_max_norm, gradient_norm, step_norm;
+  double relative_decrease, trust_region_radius, eta;
+  int linear_solver_iterations;
+  float iteration_ms;                   /* wall clock of the iteration           */
+} cb200_lm_iteration;
+
+typedef struct cb200_lm_summary {
+  double initial_cost, final_cost;
+  int num_iterations;                   /* entries written to `iterations` (incl. iteration 0) */
+  int num_successful_steps, num_unsuccessful_steps;
+  int termination_type;                 /* CB200_CONVERGENCE / NO_CONVERGENCE / FAILURE */
+  char message[256];
+  float total_ms, evaluate_ms, linear_solver_ms;
+  int num_linear_solver_iterations;
+} cb200_lm_summary;
+
+/* Program + ProgramEvaluator for SnavelyReprojectionError residuals
+ * (examples/snavely_reprojection_error.h:57-92, program_evaluator.h:189-260):
+ * observations has 2N entries in row order; cameras 9C, points 3P. */
+int cb200_bal_attach(cb200_solver* s, const double* observations);
+int cb200_bal_set_parameters(cb200_solver* s, const double* cameras, const double* points);
+int cb200_bal_get_parameters(cb200_solver* s, double* cameras, double* points);
+/* Evaluator::Evaluate at the resident parameters: cost, and with jacobian != 0 the
+ * residuals and the UNSCALED Jacobian, written straight into the solver's device
+ * arrays (as cb200_upload would). gradient (3P + 9C, J'r) may be NULL. */
+int cb200_bal_evaluate(cb200_solver* s, int jacobian, double* cost, double* gradient);
+/* the device-resident Jacobian / residuals back in the evaluator's layout (tests) */
+int cb200_download_jacobian(cb200_solver* s, double* values, double* residuals);
+/* TrustRegionMinimizer::Minimize with LevenbergMarquardtStrategy
+ * (trust_region_minimizer.cc:68-138, levenberg_marquardt_strategy.cc:69-171),
+ * starting from the resident parameters; the result replaces them. iterations may
+ * be NULL; at most max_iterations_out entries are written. */
+int cb200_lm_minimize(cb200_solver* s, const cb200_lm_options* options, cb200_lm_summary* summary,
+                      cb200_lm_iteration* iterations, int max_iterations_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -231,3 +231,55 @@ def test_venice_full_size_properties():
     r = g.isc_rhs() - g.isc_multiply(z[st.num_cols_e:])
     assert s["termination_type"] == 0, s
     assert np.linalg.norm(r) <= 1.01e-8 * np.linalg.norm(g.isc_rhs())
+
+
+# ---- widened boundary: device evaluator + trust-region loop --------------------
+
+def test_device_evaluator_matches_host_evaluator():
+    """bal_eval_kernel == the host evaluator (same dual-number model): cost, residuals, Jacobian
+    blocks, gradient J'r (program_evaluator.h:189-260)."""
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    p = m.SyntheticBAL(40, 3000, 14000, seed=3)
+    g = m.IterativeSchurComplementSolver(p.structure)
+    g.bal_attach(p.observations)
+    g.bal_set_parameters(p.cameras, p.points)
+    cost, residuals, values = p.evaluate()
+    gc, grad = g.bal_evaluate(jacobian=True)
+    gv, gr = g.download_jacobian()
+    assert abs(gc - cost) <= 1e-13 * cost
+    assert util.rel_err(gr, residuals) < 1e-12
+    assert util.rel_err(gv, values) < 1e-12
+    assert util.rel_err(grad, lmr.jacobian_transpose_times(p, values, residuals)) < 1e-12
+    c2, _ = g.bal_evaluate(jacobian=False)
+    assert abs(c2 - cost) <= 1e-13 * cost
+
+
+@pytest.mark.parametrize("eta", [1e-1, 1e-2])
+def test_lm_final_cost_matches_reference_loop(eta):
+    """north_star: final cost within 1e-8 relative at the same LM iteration count. The device loop
+    (cb200_lm_minimize: device evaluator + device linear solver) against the CPU restatement of
+    TrustRegionMinimizer + LevenbergMarquardtStrategy driving the oracle linear solver."""
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    p = m.SyntheticBAL(31, 3000, 14000, seed=7, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    st = p.structure
+    o = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=500)
+    want = lmr.minimize(p, p.cameras, p.points, lambda v, r, D, e: o.solve(v, r, D, e, -1.0), eta=eta,
+                        max_num_iterations=8)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=500)
+    g.bal_attach(p.observations)
+    g.bal_set_parameters(p.cameras, p.points)
+    got = g.lm_minimize(eta=eta, max_num_iterations=8)
+    assert got["termination_type"] == want["termination_type"]
+    assert len(got["iterations"]) == len(want["iterations"])
+    assert abs(got["initial_cost"] - want["initial_cost"]) <= 1e-12 * want["initial_cost"]
+    for a, b in zip(got["iterations"], want["iterations"]):
+        assert a["iteration"] == b["iteration"]
+        assert bool(a["step_is_successful"]) == bool(b["step_is_successful"])
+        assert a["linear_solver_iterations"] == b["linear_solver_iterations"], (a, b)
+        assert abs(a["cost"] - b["cost"]) <= 1e-8 * b["cost"], (a, b)
+    assert abs(got["final_cost"] - want["final_cost"]) <= 1e-8 * want["final_cost"]
+    assert want["final_cost"] < 0.2 * want["initial_cost"]  # the loop did minimise
+    cam, pts = g.bal_get_parameters()
+    assert util.rel_err(cam, want["cameras"]) < 1e-7 and util.rel_err(pts, want["points"]) < 1e-7
