@@ -79,6 +79,7 @@ struct cb200_solver {
   double *d_scale = nullptr;       // [3 P_loc + 9C] Jacobi scaling (points, then cameras)
   double *d_norm2 = nullptr;       // [3 P_loc + 9C] squared column norms of the unscaled Jacobian
   double *d_grad = nullptr;        // [3 P_loc + 9C] J'r
+  double *d_cam_acc = nullptr;     // privatised camera accumulators of the evaluator
   double *d_cost_partial = nullptr;
   double *d_lm_scalars = nullptr;  // cost, model, |x|^2, |delta|^2, gradient max, gradient norm^2
   double *h_lm_scalars = nullptr;  // pinned

@@ -187,6 +187,7 @@ point_stream_kernel(const StreamArgs a) {
   if (lane < 18) cu[lane] = 0.0;
   __syncwarp();
 
+  double model_acc = 0.0;  // (kModeBack) this lane's share of the model cost change
   for (int t = t_begin, i = 0; t < t_end; ++t, ++i) {
     const int s = i % L::kStages;
     unsigned char* st = wsm + s * L::kStageBytes;
@@ -358,10 +359,7 @@ point_stream_kernel(const StreamArgs a) {
       // model cost change of the step -y: m = J y for this row, b = t + F x
       const double m0 = Ei[0] * v0 + Ei[1] * v1 + Ei[2] * v2 + fz0;
       const double m1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2 + fz1;
-      double val = active ? m0 * (t0 + fz0 - 0.5 * m0) + m1 * (t1 + fz1 - 0.5 * m1) : 0.0;
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) val += __shfl_xor_sync(0xffffffffu, val, off);
-      if (lane == 0) atomicAdd(a.model, val);
+      if (active) model_acc += m0 * (t0 + fz0 - 0.5 * m0) + m1 * (t1 + fz1 - 0.5 * m1);
       continue;
     }
     // ---- w_r = t_r - E_r v (or E_r v); F_r' w_r goes to the camera accumulator ----
@@ -400,6 +398,11 @@ point_stream_kernel(const StreamArgs a) {
       }
     }
     __syncwarp();
+  }
+  if (MODE == kModeBack && a.model != nullptr) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) model_acc += __shfl_xor_sync(0xffffffffu, model_acc, off);
+    if (lane == 0) atomicAdd(a.model, model_acc);  // one atomic per warp, not per tile
   }
 }
 
