@@ -74,6 +74,7 @@ int LoadNccl(Nccl* n) {
   n->GetUniqueId = reinterpret_cast<decltype(n->GetUniqueId)>(dlsym(n->lib, "ncclGetUniqueId"));
   n->CommInitRank = reinterpret_cast<decltype(n->CommInitRank)>(dlsym(n->lib, "ncclCommInitRank"));
   n->AllReduce = reinterpret_cast<decltype(n->AllReduce)>(dlsym(n->lib, "ncclAllReduce"));
+  n->AllGather = reinterpret_cast<decltype(n->AllGather)>(dlsym(n->lib, "ncclAllGather"));
   n->CommDestroy = reinterpret_cast<decltype(n->CommDestroy)>(dlsym(n->lib, "ncclCommDestroy"));
   n->GetErrorString = reinterpret_cast<decltype(n->GetErrorString)>(dlsym(n->lib, "ncclGetErrorString"));
   if (!n->GetUniqueId || !n->CommInitRank || !n->AllReduce || !n->CommDestroy)
@@ -115,6 +116,9 @@ void cb200_destroy(cb200_solver* s) {
   if (!s) return;
   if (s->opt.device_id >= 0) cudaSetDevice(s->opt.device_id);
   if (s->stream) cudaStreamSynchronize(s->stream);
+  for (int r = 0; r < 16; ++r)
+    if (s->peer_base[r] && s->peer_base[r] != s->d_peer_buf) cudaIpcCloseMemHandle(s->peer_base[r]);
+  if (s->d_peer_buf) cudaFree(s->d_peer_buf);
   if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
   for (void* p : s->allocations) cudaFree(p);
   if (s->h_cg) cudaFreeHost(s->h_cg);
@@ -296,6 +300,43 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
                                (s->nccl.GetErrorString ? s->nccl.GetErrorString(nrc) : "error"));
       return cleanup_fail(CB200_ERR_NCCL);
     }
+  }
+  if (o.world_size > 1 && o.world_size <= kMaxPeers && s->fused_step_ok && s->nccl.AllGather &&
+      std::getenv("CB200_NO_PEER_ALLREDUCE") == nullptr) {
+    // Map every rank's partial-sum buffer into every other rank (CUDA IPC over NVLink); the handles
+    // travel through the NCCL communicator, so the C ABI needs nothing new. All ranks must take the
+    // same decision: a sum of success flags settles it.
+    const size_t qbytes = (size_t)2 * 9 * s->C * sizeof(double);
+    const size_t bytes = qbytes + 256;
+    double ok = 1.0;
+    cudaIpcMemHandle_t mine;
+    if (cudaMalloc(&s->d_peer_buf, bytes) != cudaSuccess || cudaMemset(s->d_peer_buf, 0, bytes) != cudaSuccess ||
+        cudaIpcGetMemHandle(&mine, s->d_peer_buf) != cudaSuccess) ok = 0.0;
+    std::vector<cudaIpcMemHandle_t> all(o.world_size);
+    cudaIpcMemHandle_t* d_handles = nullptr;
+    TRY(DeviceAlloc(s, &d_handles, (size_t)o.world_size));
+    if (ok != 0.0) TRY_CUDA(cudaMemcpy(d_handles + o.rank, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+    if (s->nccl.AllGather(d_handles + o.rank, d_handles, sizeof(mine), /*ncclChar*/ 0, s->nccl.comm, s->stream) != 0) {
+      Fail(CB200_ERR_NCCL, "ncclAllGather (IPC handles) failed");
+      return cleanup_fail(CB200_ERR_NCCL);
+    }
+    TRY_CUDA(cudaStreamSynchronize(s->stream));
+    TRY_CUDA(cudaMemcpy(all.data(), d_handles, all.size() * sizeof(mine), cudaMemcpyDeviceToHost));
+    for (int r = 0; r < o.world_size && ok != 0.0; ++r) {
+      if (r == o.rank) { s->peer_base[r] = s->d_peer_buf; continue; }
+      if (cudaIpcOpenMemHandle(&s->peer_base[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        s->peer_base[r] = nullptr;
+        ok = 0.0;
+        cudaGetLastError();
+      }
+    }
+    double* d_ok = nullptr;
+    TRY(DeviceAlloc(s, &d_ok, 1));
+    TRY_CUDA(cudaMemcpy(d_ok, &ok, sizeof(double), cudaMemcpyHostToDevice));
+    TRY(AllReduce(s, d_ok, 1));
+    TRY_CUDA(cudaStreamSynchronize(s->stream));
+    TRY_CUDA(cudaMemcpy(&ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost));
+    s->peer_allreduce = (ok == (double)o.world_size);
   }
 #undef TRY
 #undef TRY_CUDA

@@ -16,6 +16,8 @@
 namespace cb200 {
 
 constexpr int kStepThreads = 128;
+constexpr int kMaxPeers = 16;
+constexpr unsigned long long kPeerTimeoutNs = 4000000000ull;  // a peer rank died or fell out of step
 
 enum CgStepKind {
   kStepStart = 0,   // iteration 1 prologue: z = M^-1 r, rho, p = z          (:160-174)
@@ -40,11 +42,19 @@ struct CgStepArgs {
   int C;
   double* trace;
   int max_trace;
+  // several GPUs, fused all-reduce over NVLink peer memory: every rank publishes its folded
+  // partial in its own buffer (two slots, alternating) and reads all ranks' in rank order
+  int world, rank;
+  unsigned int epoch;            // value this launch writes to / expects in the flags
+  double* peer_q[kMaxPeers];     // [rank] -> that rank's buffer: 2 slots x 9C doubles
+  unsigned int* peer_flag[kMaxPeers];  // [rank] -> that rank's 2 flags (one per slot, 128 bytes apart)
 };
 
-// Sense-reversing grid barrier on two ints of CgState. Two barriers per launch
-// bring the flag back to 0. Requires co-resident CTAs (cooperative launch).
-__device__ __forceinline__ void GridBarrier(CgState* st, int sense) {
+// Grid barrier on two ints of CgState: bar_flag counts completed barriers (it only
+// grows), every CTA carries its own copy `gen` read at kernel entry. Safe because no
+// barrier can complete before every CTA has arrived, i.e. has read its `gen`.
+// Requires co-resident CTAs (cooperative launch).
+__device__ __forceinline__ void GridBarrier(CgState* st, unsigned int& gen) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
@@ -52,12 +62,13 @@ __device__ __forceinline__ void GridBarrier(CgState* st, int sense) {
     if (old == gridDim.x - 1) {
       st->bar_count = 0;
       __threadfence();
-      atomicExch(&st->bar_flag, (unsigned int)sense);
+      atomicExch(&st->bar_flag, gen + 1);
     } else {
-      while (*reinterpret_cast<volatile unsigned int*>(&st->bar_flag) != (unsigned int)sense) {}
+      while (*reinterpret_cast<volatile unsigned int*>(&st->bar_flag) == gen) {}
     }
     __threadfence();
   }
+  ++gen;
   __syncthreads();
 }
 
@@ -65,14 +76,14 @@ __device__ __forceinline__ void GridBarrier(CgState* st, int sense) {
 // `row0` selects the rows of CgState::partial: the two reductions of one launch
 // use different rows, so a fast CTA cannot overwrite what a slow one still reads.
 template <int K>
-__device__ __forceinline__ void GridSums(CgState* st, int sense, int row0, const double* vals,
+__device__ __forceinline__ void GridSums(CgState* st, unsigned int& gen, int row0, const double* vals,
                                          double* sums, double* sbuf) {
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     const double s = BlockSum(vals[k], sbuf);
     if (threadIdx.x == 0) st->partial[row0 + k][blockIdx.x] = s;
   }
-  GridBarrier(st, sense);
+  GridBarrier(st, gen);
   if (threadIdx.x < K) {
     double s = 0.0;
     const volatile double* part = st->partial[row0 + threadIdx.x];
@@ -86,7 +97,7 @@ template <int KIND, int PRECOND>
 __global__ void __launch_bounds__(kStepThreads)
 cg_step_kernel(const CgStepArgs a) {
   CgState* st = a.st;
-  if (st->done) return;
+  if (st->done || st->peer_timeout) return;
   __shared__ double sbuf[8];
   __shared__ double sums[4];
   // scalars of the iteration, read before anything is written (CTA 0 writes after barrier 1)
@@ -95,6 +106,7 @@ cg_step_kernel(const CgStepArgs a) {
   double Q0 = st->Q0;
   const double q_tol = st->q_tolerance, tol_r = st->tol_r;
   const int min_it = st->min_iterations, max_it = st->max_iterations;
+  unsigned int gen = *reinterpret_cast<volatile unsigned int*>(&st->bar_flag);
   const bool writer = blockIdx.x == 0 && threadIdx.x == 0;
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   const bool on = c < a.C;
@@ -131,6 +143,46 @@ cg_step_kernel(const CgStepArgs a) {
           for (int k = 0; k < 5; ++k) y[k] = make_double2(0.0, 0.0);
         }
       }
+    }
+    if (a.world > 1 && a.q == nullptr) {
+      // ---- all-reduce of q over the ranks through peer memory ----
+      const int slot = a.epoch & 1u;
+      const size_t n9 = (size_t)9 * a.C;
+      if (on) {
+        double* mine = a.peer_q[a.rank] + slot * n9 + o9;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) mine[k] = q[k];
+      }
+      GridBarrier(st, gen);  // every CTA of this rank has published
+      if (threadIdx.x == 0) {
+        if (blockIdx.x == 0) {
+          __threadfence_system();
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(a.epoch) : "memory");
+        }
+        for (int r = 0; r < a.world; ++r) {
+          if (r == a.rank) continue;
+          unsigned int seen;
+          unsigned long long t0, t1;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+          do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[r] + slot * 32) : "memory");
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }  // never hang the GPU
+          } while (seen != a.epoch);
+        }
+      }
+      __syncthreads();
+      if (on) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) q[k] = 0.0;
+        for (int r = 0; r < a.world; ++r) {  // rank order: the same sum, bit for bit, on every rank
+          const double* theirs = a.peer_q[r] + slot * n9 + o9;
+#pragma unroll
+          for (int k = 0; k < 9; ++k) q[k] += __ldcg(theirs + k);
+        }
+      }
+    }
+    if (on) {
       // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
       if (a.Df != nullptr) {
 #pragma unroll
@@ -143,21 +195,19 @@ cg_step_kernel(const CgStepArgs a) {
     double v[3] = {0.0, 0.0, 0.0};
 #pragma unroll
     for (int k = 0; k < 9; ++k) { v[0] += p[k] * q[k]; v[1] += p[k] * p[k]; v[2] += q[k] * q[k]; }
-    GridSums<3>(st, 1, 0, v, sums, sbuf);
+    GridSums<3>(st, gen, 0, v, sums, sbuf);
     const double pq = sums[0];
     if (pq <= 0.0 || isinf(pq)) {
       if (writer) {
         st->pq = pq; st->norm_p = sqrt(sums[1]); st->norm_q = sqrt(sums[2]);
         Finish(st, CB200_LINEAR_SOLVER_NO_CONVERGENCE, kReasonIndefinite);
       }
-      GridBarrier(st, 0);
       return;
     }
     alpha = rho / pq;
     if (writer) { st->pq = pq; st->alpha = alpha; }
     if (isinf(alpha)) {
       if (writer) Finish(st, CB200_LINEAR_SOLVER_FAILURE, kReasonAlphaFailure);
-      GridBarrier(st, 0);
       return;
     }
     // ---- x += alpha p (:216) ----
@@ -170,10 +220,7 @@ cg_step_kernel(const CgStepArgs a) {
         if (KIND == kStepResetA) a.x10[o10 + k] = x[k];  // S x comes next
       }
     }
-    if (KIND == kStepResetA) {
-      GridBarrier(st, 0);
-      return;
-    }
+    if (KIND == kStepResetA) return;
   }
   // ---- residual (:221-227) ----
   if (on) {
@@ -205,9 +252,7 @@ cg_step_kernel(const CgStepArgs a) {
     v[0] += r[k] * z[k];
     if (KIND != kStepStart && on) { v[1] += x[k] * (a.rhs[o9 + k] + r[k]); v[2] += r[k] * r[k]; }
   }
-  // kinds without the p'q reduction run this one as their first barrier and close with a third
-  constexpr bool kTailBarrier = (KIND == kStepStart || KIND == kStepResetB);
-  GridSums<3>(st, kTailBarrier ? 1 : 0, 3, v, sums, sbuf);
+  GridSums<3>(st, gen, 3, v, sums, sbuf);
   int next_it = it;
   if (KIND != kStepStart) {
     // ---- Q1, zeta, |r|, iteration limit (:229-300) ----
@@ -223,10 +268,7 @@ cg_step_kernel(const CgStepArgs a) {
       if (reason != kReasonZetaConvergence) st->Q0 = Q1;
       if (term >= 0) Finish(st, term, reason);
     }
-    if (term >= 0) {
-      if (kTailBarrier) GridBarrier(st, 0);
-      return;
-    }
+    if (term >= 0) return;
   }
   // ---- prologue of the next iteration: rho, beta, p (:163-188) ----
   next_it = it + 1;
@@ -244,10 +286,7 @@ cg_step_kernel(const CgStepArgs a) {
     if (next_it > 1 && fail != kReasonRhoFailure) st->beta = beta;
     if (fail) Finish(st, CB200_LINEAR_SOLVER_FAILURE, fail);
   }
-  if (fail) {
-    if (kTailBarrier) GridBarrier(st, 0);
-    return;
-  }
+  if (fail) return;
   if (on) {
 #pragma unroll
     for (int k = 0; k < 9; ++k) {
@@ -256,7 +295,6 @@ cg_step_kernel(const CgStepArgs a) {
       a.x10[o10 + k] = pk;  // S p comes next
     }
   }
-  if (kTailBarrier) GridBarrier(st, 0);  // leave the barrier flag at 0 for the next launch
 }
 
 }  // namespace cb200

@@ -21,6 +21,7 @@ struct Nccl {
   int (*GetUniqueId)(UniqueId*) = nullptr;
   int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
   int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
@@ -86,6 +87,11 @@ struct cb200_solver {
   int eval_blocks = 0;
 
   cb200::Nccl nccl;
+  // fused all-reduce of the PCG step over NVLink peer memory (cg_step.cuh); null = NCCL path
+  void* d_peer_buf = nullptr;                 // this rank's 2 slots x 9C doubles + 2 flags
+  void* peer_base[16] = {};                   // every rank's buffer as mapped here (own = d_peer_buf)
+  unsigned int peer_epoch = 0;
+  bool peer_allreduce = false;
   int launches = 0;
   std::vector<void*> allocations;
 };
