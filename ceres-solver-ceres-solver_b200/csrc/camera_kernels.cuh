@@ -24,7 +24,7 @@ constexpr int kChunkThreads = 128;
 // One CTA per chunk (<= kChunkObs rows of one camera, listed camera-major in
 // cam_perm); out: the 45 upper-triangle sums of the chunk.
 // ----------------------------------------------------------------------------
-constexpr int kChunkDepth = 3;     // rows in flight per thread (cp.async pipeline)
+constexpr int kChunkDepth = 3;     // 32-row groups in flight per warp (cp.async pipeline)
 constexpr int kChunkSlot = 176;    // bytes per staged row: F (144) + weights (24), 16-byte aligned
 constexpr int kChunkSmemBytes = kChunkDepth * kChunkThreads * kChunkSlot;
 
@@ -38,10 +38,13 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// The rows of a camera are scattered over the point-major Jacobian, so every
-// thread streams its own rows through a private kChunkDepth-deep cp.async ring
-// in shared memory (a thread only ever reads what it copied itself: no CTA
-// barrier in the loop) while it accumulates the 45 upper-triangle products.
+// The rows of a camera are scattered over the point-major Jacobian. Every warp
+// streams groups of 32 rows through its own kChunkDepth-deep cp.async ring; a
+// group's 32 x 144 bytes of F are fetched as 288 16-byte pieces, lane l taking
+// pieces j*32 + l, so that one request touches the few cache lines of 3-4 rows
+// instead of 32 (the L1 tag stage looks up one line per cycle). After the
+// group has landed each lane owns one row and accumulates its 45 upper-triangle
+// products. No CTA barrier in the loop.
 template <bool WEIGHTED>
 __global__ void __launch_bounds__(kChunkThreads)
 camera_block_kernel(const double* __restrict__ F, const double* __restrict__ weights,
@@ -49,19 +52,33 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
                     double* __restrict__ chunk_partial) {
   extern __shared__ __align__(16) unsigned char ring[];
   __shared__ double sred[kChunkThreads / 32][45];
+  constexpr int kWarps = kChunkThreads / 32;
+  constexpr int kGroupBytes = 32 * kChunkSlot;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int begin = chunk_begin[blockIdx.x], end = chunk_begin[blockIdx.x + 1];
-  unsigned char* mine = ring + threadIdx.x * kChunkSlot;
-  auto slot = [&](int d) { return mine + d * (kChunkThreads * kChunkSlot); };
-  auto issue = [&](int i, int d, int r) {  // r = cam_perm[i], loaded by the caller ahead of time
-    if (i < end) {
-      const double* f = F + (size_t)r * 18;
-      unsigned char* dst = slot(d);
+  unsigned char* mine = ring + warp * (kChunkDepth * kGroupBytes);
+  // group g of this warp = rows [begin + (g * kWarps + warp) * 32, +32)
+  auto group_row0 = [&](int g) { return begin + (g * kWarps + warp) * 32; };
+  auto load_index = [&](int g) {
+    const int i = group_row0(g) + lane;
+    return i < end ? __ldg(cam_perm + i) : -1;
+  };
+  auto issue = [&](int d, int r_own) {  // r_own: row of lane's slot in the group, -1 past the end
+    unsigned char* dst = mine + d * kGroupBytes;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) cp_async16(dst + 16 * k, f + 2 * k);
-      if (WEIGHTED) {
-        const double* w = weights + (size_t)r * 3;
+    for (int j = 0; j < 9; ++j) {
+      const int idx = j * 32 + lane;
+      const int o = idx / 9, pc = idx - 9 * o;
+      const int r = __shfl_sync(0xffffffffu, r_own, o);
+      if (r >= 0) cp_async16(dst + o * kChunkSlot + 16 * pc, F + (size_t)r * 18 + 2 * pc);
+    }
+    if (WEIGHTED) {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) cp_async8(dst + 144 + 8 * k, w + k);
+      for (int j = 0; j < 3; ++j) {
+        const int idx = j * 32 + lane;
+        const int o = idx / 3, pc = idx - 3 * o;
+        const int r = __shfl_sync(0xffffffffu, r_own, o);
+        if (r >= 0) cp_async8(dst + o * kChunkSlot + 144 + 8 * pc, weights + (size_t)r * 3 + pc);
       }
     }
     cp_async_commit();
@@ -69,32 +86,32 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
   double acc[45];
 #pragma unroll
   for (int k = 0; k < 45; ++k) acc[k] = 0.0;
-  const int first = begin + threadIdx.x;
+  const int rows = end - begin;
+  const int my_groups = (rows - warp * 32 + kWarps * 32 - 1) / (kWarps * 32);  // groups with >= 1 row (<= 0: none)
 #pragma unroll
-  for (int d = 0; d < kChunkDepth; ++d) {
-    const int i = first + d * kChunkThreads;
-    issue(i, d, i < end ? cam_perm[i] : 0);
-  }
-  // row index of the next refill: loaded one iteration before the copy that needs it
-  int r_next = (first + kChunkDepth * kChunkThreads < end) ? cam_perm[first + kChunkDepth * kChunkThreads] : 0;
+  for (int d = 0; d < kChunkDepth; ++d) issue(d, d < my_groups ? load_index(d) : -1);
+  // row indices of the next refill: loaded one iteration before the copies that need them
+  int r_next = kChunkDepth < my_groups ? load_index(kChunkDepth) : -1;
   int d = 0;
-  for (int i = first; i < end; i += kChunkThreads) {
+  for (int g = 0; g < my_groups; ++g) {
     cp_async_wait<kChunkDepth - 1>();
-    const double2* f2 = reinterpret_cast<const double2*>(slot(d));
+    __syncwarp();  // every lane's pieces of group g have landed
+    const bool live = group_row0(g) + lane < end;
+    const unsigned char* row = mine + d * kGroupBytes + lane * kChunkSlot;
+    const double2* f2 = reinterpret_cast<const double2*>(row);
     double f[18];
 #pragma unroll
     for (int k = 0; k < 9; ++k) { const double2 v = f2[k]; f[2 * k] = v.x; f[2 * k + 1] = v.y; }
     double w00 = 1.0, w01 = 0.0, w11 = 1.0;
     if (WEIGHTED) {
-      const double* w = reinterpret_cast<const double*>(slot(d) + 144);
+      const double* w = reinterpret_cast<const double*>(row + 144);
       w00 = w[0]; w01 = w[1]; w11 = w[2];
     }
-    issue(i + kChunkDepth * kChunkThreads, d, r_next);  // refill the slot just read
-    {
-      const int i2 = i + (kChunkDepth + 1) * kChunkThreads;
-      r_next = (i2 < end) ? cam_perm[i2] : 0;
-    }
+    __syncwarp();  // the slot has been read by all lanes: refill it
+    issue(d, r_next);
+    r_next = (g + kChunkDepth + 1 < my_groups) ? load_index(g + kChunkDepth + 1) : -1;
     d = (d + 1 == kChunkDepth) ? 0 : d + 1;
+    if (!live) continue;  // (stale bytes of an earlier group)
     double g0[9], g1[9];  // W * F
     if (WEIGHTED) {
 #pragma unroll
@@ -113,7 +130,6 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
       for (int j = i2; j < 9; ++j) { acc[q] += f[i2] * g0[j] + f[9 + i2] * g1[j]; ++q; }
   }
   cp_async_wait<0>();
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int k = 0; k < 45; ++k) {
     double v = acc[k];

@@ -22,6 +22,7 @@
 namespace cb200 {
 
 constexpr int kTileObs = 32;  // rows per tile of the fused per-point kernels: one lane each
+constexpr int kTilePoints = 16;  // points (= (E'E)^-1 blocks staged) per tile; real tracks have >= 2 rows
 constexpr int kChunkedPointRows = 256;  // points of 33..256 rows run as chunk tiles inside the stream kernel
 // flags in TileMeta::np above the point count (low 8 bits)
 constexpr int kTileKindShift = 8;        // bits 8-9: 0 whole points, 1 first-pass chunk, 2 second-pass chunk
@@ -199,7 +200,7 @@ inline TilePlan PlanTiles(const int* row_start /* local, P_loc+1 */, const int* 
       continue;
     }
     if (open_rows + len > kTileObs) emit();
-    if (!members.empty() && p - members.front() >= kTileObs) emit();  // np <= kTileObs (empty points between)
+    if (!members.empty() && p - members.front() >= kTilePoints) emit();  // np <= kTilePoints (empty points between)
     members.push_back(p);
     open_rows += len;
   }

@@ -71,7 +71,7 @@ struct StreamLayout {
   static constexpr int kOffF = kOffE + kTileObs * 48;
   static constexpr int kOffMeta = kOffF + kTileObs * 144;
   static constexpr int kOffInv = kOffMeta + kMetaBytes;
-  static constexpr int kOffB = kOffInv + (kLoadsInv ? kTileObs * 48 : 0);
+  static constexpr int kOffB = kOffInv + (kLoadsInv ? kTilePoints * 48 : 0);
   static constexpr int kStageBytes = kOffB + (kUsesB ? kTileObs * 16 : 0);
   // per warp: stages, then the 32 x 10 transposition scratch, then the barriers
   static constexpr int kOffX = kStages * kStageBytes;

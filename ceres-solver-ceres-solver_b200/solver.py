@@ -133,7 +133,8 @@ def lib():
     """Load libceres_b200_schur.so (building it if the sources are newer)."""
     global _LIB
     if _LIB is None:
-        path = _build.build_cuda()
+        # CB200_LIBRARY: a differently-built copy of the same library (kernel experiments, tools/build_variant.py)
+        path = os.environ.get("CB200_LIBRARY") or _build.build_cuda()
         L = ctypes.CDLL(path)
         for name, (res, args) in SYMBOLS.items():
             f = getattr(L, name)  # AttributeError if the library lacks a declared symbol
