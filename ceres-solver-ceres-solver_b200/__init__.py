@@ -10,4 +10,4 @@ from . import _build  # noqa: F401
 from .solver import (IDENTITY, JACOBI, SCHUR_JACOBI, SCHUR_POWER_SERIES_EXPANSION,  # noqa: F401
                      TERMINATION, B200Error, BlockStructure, IterativeSchurComplementSolver,
                      nccl_unique_id, shard_plan)
-from .bal import SHAPES, SyntheticBAL  # noqa: F401
+from .bal import SHAPES, BALFile, SyntheticBAL  # noqa: F401

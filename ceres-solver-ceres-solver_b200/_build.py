@@ -45,7 +45,7 @@ def build_cuda(force=False, verbose=False):
 
 def build_bal(force=False):
     src = os.path.join(CSRC, "synthetic_bal.cc")
-    if not force and not _stale(LIB_BAL, [src, os.path.join(CSRC, "snavely_model.h")]):
+    if not force and not _stale(LIB_BAL, [src, os.path.join(CSRC, "snavely_model.h"), os.path.join(CSRC, "bal_io.h")]):
         return LIB_BAL
     # x86-64-v3 (not -march=native): the .so is built here and run on the GPU box
     subprocess.run(["g++", "-O3", "-march=x86-64-v3", "-std=c++17", "-fopenmp", "-fPIC", "-shared",
@@ -53,8 +53,25 @@ def build_bal(force=False):
     return LIB_BAL
 
 
+CLI = os.path.join(HERE, "bin", "bundle_adjuster")
+
+
+def build_cli(force=False):
+    """tools/bundle_adjuster.cc: the reference's examples/bundle_adjuster flow over the C ABI."""
+    src = os.path.join(HERE, "..", "tools", "bundle_adjuster.cc")
+    deps = [src, os.path.join(CSRC, "bal_io.h"), os.path.join(CSRC, "snavely_model.h"),
+            os.path.join(HERE, "..", "include", "ceres_b200_schur.h"), LIB_CUDA]
+    build_cuda()
+    if not force and not _stale(CLI, deps):
+        return CLI
+    os.makedirs(os.path.dirname(CLI), exist_ok=True)
+    subprocess.run(["g++", "-O2", "-std=c++17", "-o", CLI, src, "-L" + HERE, "-lceres_b200_schur",
+                    "-Wl,-rpath,$ORIGIN/..", "-ldl", "-lpthread"], check=True)
+    return CLI
+
+
 def build_all(force=False):
-    return build_cuda(force), build_bal(force)
+    return build_cuda(force), build_bal(force), build_cli(force)
 
 
 if __name__ == "__main__":

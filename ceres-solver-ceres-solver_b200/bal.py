@@ -36,6 +36,21 @@ def lib():
                                          ctypes.c_ulonglong] + [ctypes.c_double] * 4 + [_dp, _dp, _dp]
         L.bal_evaluate.restype = ctypes.c_double
         L.bal_evaluate.argtypes = [ctypes.c_int, ctypes.c_longlong, _ip, _ip, _dp, _dp, _dp, _dp, _dp, _dp]
+        L.bal_file_error.restype = ctypes.c_char_p
+        L.bal_file_open.restype = ctypes.c_int
+        L.bal_file_open.argtypes = [ctypes.c_char_p, ctypes.POINTER(ctypes.c_void_p), _ip, _ip, _ip]
+        L.bal_file_fetch.restype = None
+        L.bal_file_fetch.argtypes = [ctypes.c_void_p, _ip, _ip, _dp, _dp, _dp]
+        L.bal_file_write.restype = ctypes.c_int
+        L.bal_file_write.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, _ip, _ip, _dp, _dp, _dp]
+        L.bal_file_write_ply.restype = ctypes.c_int
+        L.bal_file_write_ply.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, _dp, _dp]
+        L.bal_normalize.restype = None
+        L.bal_normalize.argtypes = [ctypes.c_int, ctypes.c_int, _dp, _dp]
+        L.bal_perturb.restype = None
+        L.bal_perturb.argtypes = [ctypes.c_int, ctypes.c_int] + [ctypes.c_double] * 3 + [_dp, _dp]
+        L.bal_group_by_point.restype = None
+        L.bal_group_by_point.argtypes = [ctypes.c_int, ctypes.c_int, _ip, _ip, _ip]
         _LIB = L
     return _LIB
 
@@ -70,6 +85,19 @@ class SyntheticBAL:
             lib().bal_synth_geometry(C, P, N, _i(self.point_row_start), _i(self.cam_idx), seed, pixel_sigma,
                                      rotation_sigma, translation_sigma, point_sigma, _d(self.cameras),
                                      _d(self.points), _d(self.observations))
+
+    @classmethod
+    def from_arrays(cls, num_cameras, point_row_start, cam_idx, observations, cameras, points):
+        """A problem given outright (rows grouped by point), e.g. from a BAL file."""
+        self = cls.__new__(cls)
+        self.point_row_start = np.ascontiguousarray(point_row_start, dtype=np.int32)
+        self.cam_idx = np.ascontiguousarray(cam_idx, dtype=np.int32)
+        self.C, self.P, self.N = int(num_cameras), len(self.point_row_start) - 1, len(self.cam_idx)
+        self.structure = BlockStructure.bal(self.point_row_start, self.cam_idx, self.C)
+        self.observations = np.ascontiguousarray(observations, dtype=np.float64)
+        self.cameras = np.ascontiguousarray(cameras, dtype=np.float64)
+        self.points = np.ascontiguousarray(points, dtype=np.float64)
+        return self
 
     @classmethod
     def named(cls, name, scale=1.0, **kw):
@@ -138,3 +166,64 @@ class SyntheticBAL:
         xe = x[:3 * P].reshape(P, 3)[row_point]
         xf = x[3 * P:].reshape(self.C, 9)[self.cam_idx]
         return (np.einsum("nij,nj->ni", E, xe) + np.einsum("nij,nj->ni", F, xf)).reshape(-1)
+
+
+class BALFile:
+    """A Bundle Adjustment in the Large problem file with the semantics of the reference's
+    example loader (examples/bal_problem.cc:73-333, angle-axis cameras): read / write / PLY
+    export / Normalize / Perturb. The arithmetic is csrc/bal_io.h."""
+
+    def __init__(self, camera_index, point_index, observations, cameras, points):
+        self.camera_index = np.ascontiguousarray(camera_index, dtype=np.int32)
+        self.point_index = np.ascontiguousarray(point_index, dtype=np.int32)
+        self.observations = np.ascontiguousarray(observations, dtype=np.float64)
+        self.cameras = np.ascontiguousarray(cameras, dtype=np.float64)
+        self.points = np.ascontiguousarray(points, dtype=np.float64)
+        self.num_cameras = len(self.cameras) // 9
+        self.num_points = len(self.points) // 3
+        self.num_observations = len(self.camera_index)
+
+    @classmethod
+    def read(cls, path):
+        h = ctypes.c_void_p()
+        c, p, n = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        if lib().bal_file_open(os.fsencode(path), ctypes.byref(h), ctypes.byref(c), ctypes.byref(p), ctypes.byref(n)):
+            raise ValueError(lib().bal_file_error().decode())
+        ci, pi = np.empty(n.value, np.int32), np.empty(n.value, np.int32)
+        obs, cams, pts = np.empty(2 * n.value), np.empty(9 * c.value), np.empty(3 * p.value)
+        lib().bal_file_fetch(h, _i(ci), _i(pi), _d(obs), _d(cams), _d(pts))
+        return cls(ci, pi, obs, cams, pts)
+
+    def write(self, path):
+        if lib().bal_file_write(os.fsencode(path), self.num_cameras, self.num_points, self.num_observations,
+                                _i(self.camera_index), _i(self.point_index), _d(self.observations),
+                                _d(self.cameras), _d(self.points)):
+            raise OSError(lib().bal_file_error().decode())
+
+    def write_ply(self, path):
+        if lib().bal_file_write_ply(os.fsencode(path), self.num_cameras, self.num_points, _d(self.cameras),
+                                    _d(self.points)):
+            raise OSError(lib().bal_file_error().decode())
+
+    def normalize(self):
+        lib().bal_normalize(self.num_cameras, self.num_points, _d(self.cameras), _d(self.points))
+
+    def perturb(self, rotation_sigma, translation_sigma, point_sigma):
+        lib().bal_perturb(self.num_cameras, self.num_points, rotation_sigma, translation_sigma, point_sigma,
+                          _d(self.cameras), _d(self.points))
+
+    def problem(self):
+        """Rows grouped by point, as the Schur ordering arranges them (reorder_program.cc:536-539):
+        a SyntheticBAL-shaped problem (structure, observations in row order, parameters)."""
+        order = np.empty(self.num_observations, np.int32)
+        row_start = np.empty(self.num_points + 1, np.int32)
+        lib().bal_group_by_point(self.num_points, self.num_observations, _i(self.point_index), _i(order), _i(row_start))
+        obs = self.observations.reshape(-1, 2)[order].reshape(-1)
+        return SyntheticBAL.from_arrays(self.num_cameras, row_start, self.camera_index[order], obs,
+                                        self.cameras.copy(), self.points.copy())
+
+    @classmethod
+    def from_problem(cls, p):
+        """The file form of a (synthetic) problem: observations listed point by point."""
+        point_index = np.repeat(np.arange(p.P, dtype=np.int32), np.diff(p.point_row_start))
+        return cls(p.cam_idx, point_index, p.observations, p.cameras, p.points)

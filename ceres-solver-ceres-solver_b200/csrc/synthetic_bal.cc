@@ -20,9 +20,11 @@
 #include <cstring>
 #include <numeric>
 #include <random>
+#include <string>
 #include <vector>
 
 #include "snavely_model.h"
+#include "bal_io.h"
 
 using namespace cb200_model;
 
@@ -183,6 +185,75 @@ double bal_evaluate(int P, long long N, const int* point_row_start, const int* c
     }
   }
   return cost;
+}
+
+// ---- BAL problem files (bal_io.h) for the Python side ------------------------------------
+// Two-step read: bal_file_open parses the file and returns a handle + the counts, the
+// caller allocates, bal_file_fetch copies out and frees the handle. Non-zero = error
+// (message via bal_file_error).
+static thread_local std::string g_bal_error;
+const char* bal_file_error() { return g_bal_error.c_str(); }
+
+int bal_file_open(const char* filename, void** handle, int* num_cameras, int* num_points, int* num_observations) {
+  auto* p = new cb200_bal::BalProblem;
+  g_bal_error = cb200_bal::Read(filename, p);
+  if (!g_bal_error.empty()) { delete p; return 1; }
+  *handle = p;
+  *num_cameras = p->num_cameras; *num_points = p->num_points; *num_observations = p->num_observations;
+  return 0;
+}
+void bal_file_fetch(void* handle, int* camera_index, int* point_index, double* observations, double* cameras,
+                    double* points) {
+  auto* p = static_cast<cb200_bal::BalProblem*>(handle);
+  std::copy(p->camera_index.begin(), p->camera_index.end(), camera_index);
+  std::copy(p->point_index.begin(), p->point_index.end(), point_index);
+  std::copy(p->observations.begin(), p->observations.end(), observations);
+  std::copy(p->cameras.begin(), p->cameras.end(), cameras);
+  std::copy(p->points.begin(), p->points.end(), points);
+  delete p;
+}
+static cb200_bal::BalProblem MakeBal(int C, int P, int N, const int* camera_index, const int* point_index,
+                                     const double* observations, const double* cameras, const double* points) {
+  cb200_bal::BalProblem p;
+  p.num_cameras = C; p.num_points = P; p.num_observations = N;
+  if (camera_index) p.camera_index.assign(camera_index, camera_index + N);
+  if (point_index) p.point_index.assign(point_index, point_index + N);
+  if (observations) p.observations.assign(observations, observations + 2 * (size_t)N);
+  p.cameras.assign(cameras, cameras + 9 * (size_t)C);
+  p.points.assign(points, points + 3 * (size_t)P);
+  return p;
+}
+int bal_file_write(const char* filename, int C, int P, int N, const int* camera_index, const int* point_index,
+                   const double* observations, const double* cameras, const double* points) {
+  g_bal_error = cb200_bal::Write(filename, MakeBal(C, P, N, camera_index, point_index, observations, cameras, points));
+  return g_bal_error.empty() ? 0 : 1;
+}
+int bal_file_write_ply(const char* filename, int C, int P, const double* cameras, const double* points) {
+  g_bal_error = cb200_bal::WritePly(filename, MakeBal(C, P, 0, nullptr, nullptr, nullptr, cameras, points));
+  return g_bal_error.empty() ? 0 : 1;
+}
+void bal_normalize(int C, int P, double* cameras, double* points) {
+  cb200_bal::BalProblem p = MakeBal(C, P, 0, nullptr, nullptr, nullptr, cameras, points);
+  cb200_bal::Normalize(&p);
+  std::copy(p.cameras.begin(), p.cameras.end(), cameras);
+  std::copy(p.points.begin(), p.points.end(), points);
+}
+void bal_perturb(int C, int P, double rotation_sigma, double translation_sigma, double point_sigma, double* cameras,
+                 double* points) {
+  cb200_bal::BalProblem p = MakeBal(C, P, 0, nullptr, nullptr, nullptr, cameras, points);
+  cb200_bal::Perturb(&p, rotation_sigma, translation_sigma, point_sigma);
+  std::copy(p.cameras.begin(), p.cameras.end(), cameras);
+  std::copy(p.points.begin(), p.points.end(), points);
+}
+// order[N], row_start[P + 1]: see cb200_bal::GroupByPoint
+void bal_group_by_point(int P, int N, const int* point_index, int* order, int* row_start) {
+  cb200_bal::BalProblem p;
+  p.num_points = P; p.num_observations = N;
+  p.point_index.assign(point_index, point_index + N);
+  std::vector<int> o, r;
+  cb200_bal::GroupByPoint(p, &o, &r);
+  std::copy(o.begin(), o.end(), order);
+  std::copy(r.begin(), r.end(), row_start);
 }
 
 }  // extern "C"

@@ -283,3 +283,44 @@ def test_lm_final_cost_matches_reference_loop(eta):
     assert want["final_cost"] < 0.2 * want["initial_cost"]  # the loop did minimise
     cam, pts = g.bal_get_parameters()
     assert util.rel_err(cam, want["cameras"]) < 1e-7 and util.rel_err(pts, want["points"]) < 1e-7
+
+
+def test_bundle_adjuster_cli_matches_reference_loop(tmp_path):
+    """the bundle_adjuster CLI (BAL file -> Normalize -> Perturb -> LM with
+    ITERATIVE_SCHUR on the device) against the same flow on the CPU: oracle/bal_reference-checked
+    file handling + the restated trust-region loop + the oracle linear solver."""
+    import re
+    import subprocess
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    p = m.SyntheticBAL(23, 1500, 7000, seed=5, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    m.BALFile.from_problem(p).write(tmp_path / "in.txt")
+    cli = m._build.build_cli()
+    r = subprocess.run([cli, f"--input={tmp_path / 'in.txt'}", "--num_iterations=6", "--eta=1e-2",
+                        "--preconditioner=schur_jacobi", f"--final_bal={tmp_path / 'out.txt'}",
+                        f"--final_ply={tmp_path / 'out.ply'}"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    initial = float(re.search(r"Initial\s+(\S+)", r.stdout).group(1))
+    final = float(re.search(r"Final\s+(\S+)", r.stdout).group(1))
+    rows = re.findall(r"^\s*(\d+)\s+(\S+e[+-]\d+)\s+\S+\s+\S+\s+\S+\s+\S+\s+\S+\s+(\d+)\s+\S+$", r.stdout, re.M)
+    # the same flow on the CPU
+    f = m.BALFile.read(tmp_path / "in.txt")
+    f.normalize()
+    f.perturb(0.0, 0.0, 0.0)
+    q = f.problem()
+    o = ob.Oracle(util.oracle_structure(q.structure), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI,
+                  max_num_iterations=500)
+    want = lmr.minimize(q, q.cameras, q.points, lambda v, rr, D, e: o.solve(v, rr, D, e, -1.0), eta=1e-2,
+                        max_num_iterations=6, function_tolerance=1e-16, gradient_tolerance=1e-16,
+                        parameter_tolerance=1e-16)
+    assert abs(initial - want["initial_cost"]) <= 2e-6 * want["initial_cost"]  # printed with 7 digits
+    assert abs(final - want["final_cost"]) <= 2e-6 * want["final_cost"]
+    assert len(rows) == len(want["iterations"])
+    for (it, cost, ls), b in zip(rows, want["iterations"]):
+        assert int(it) == b["iteration"] and int(ls) == b["linear_solver_iterations"], (it, ls, b)
+    # the refined problem, written with %.16g, carries the full-precision answer
+    out = m.BALFile.read(tmp_path / "out.txt")
+    assert util.rel_err(out.cameras, want["cameras"]) < 1e-7 and util.rel_err(out.points, want["points"]) < 1e-7
+    c_out, _, _ = out.problem().evaluate(jacobian=False)
+    assert abs(c_out - want["final_cost"]) <= 1e-8 * want["final_cost"]
+    assert open(tmp_path / "out.ply").readline().strip() == "ply"
