@@ -83,12 +83,44 @@ int LoadNccl(Nccl* n) {
 }
 
 // Sum a device buffer over all ranks (camera-sized data only).
-int AllReduce(cb200_solver* s, double* buf, size_t count) {
+// an environment switch is on when it is set to anything but "" or "0"
+bool EnvFlag(const char* name) {
+  const char* e = std::getenv(name);
+  return e != nullptr && e[0] != '\0' && !(e[0] == '0' && e[1] == '\0');
+}
+
+int NcclAllReduce(cb200_solver* s, double* buf, size_t count) {
   if (s->opt.world_size <= 1) return CB200_OK;
   const int rc = s->nccl.AllReduce(buf, buf, count, /*ncclDouble*/ 8, /*ncclSum*/ 0, s->nccl.comm, s->stream);
   if (rc != 0)
     return Fail(CB200_ERR_NCCL, std::string("ncclAllReduce: ") +
                                     (s->nccl.GetErrorString ? s->nccl.GetErrorString(rc) : "error"));
+  return CB200_OK;
+}
+
+void FillPeerRefs(cb200_solver* s, PeerRefs* p) {
+  p->world = s->opt.world_size; p->rank = s->opt.rank;
+  p->epoch = ++s->peer_epoch;
+  p->slot_stride = s->peer_slot;
+  for (int r = 0; r < p->world; ++r) {
+    p->base[r] = reinterpret_cast<double*>(s->peer_base[r]);
+    p->flag[r] = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(s->peer_base[r]) +
+                                                 2 * s->peer_slot * sizeof(double));
+  }
+}
+
+// Sum over the ranks, in place. Peer-memory path (rank-ordered, deterministic, two small
+// kernels) when the buffers are mapped, NCCL otherwise.
+int AllReduce(cb200_solver* s, double* buf, size_t count) {
+  if (s->opt.world_size <= 1) return CB200_OK;
+  if (!s->peer_allreduce || count > s->peer_slot) return NcclAllReduce(s, buf, count);
+  PeerRefs p;
+  FillPeerRefs(s, &p);
+  const int grid = (int)std::min<size_t>(64, (count + 255) / 256);
+  peer_publish_kernel<<<grid, 256, 0, s->stream>>>(p, buf, count, s->d_cg);
+  peer_sum_kernel<<<grid, 256, 0, s->stream>>>(p, buf, count, s->d_cg);
+  s->launches += 2;
+  if (cudaGetLastError() != cudaSuccess) return Fail(CB200_ERR_CUDA, "peer all-reduce launch failed");
   return CB200_OK;
 }
 
@@ -288,7 +320,7 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     TRY_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_step_kernel<kStepNormal, 1>, kStepThreads, 0));
     const int ctas = Blocks(s->C, kStepThreads);
     s->fused_step_ok = coop != 0 && ctas <= per_sm * s->num_sms && ctas <= kMaxVecBlocks &&
-                       std::getenv("CB200_NO_FUSED_STEP") == nullptr;
+                       !EnvFlag("CB200_NO_FUSED_STEP");
   }
   if (o.world_size > 1) {
     TRY(LoadNccl(&s->nccl));
@@ -302,11 +334,12 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     }
   }
   if (o.world_size > 1 && o.world_size <= kMaxPeers && s->fused_step_ok && s->nccl.AllGather &&
-      std::getenv("CB200_NO_PEER_ALLREDUCE") == nullptr) {
+      !EnvFlag("CB200_NO_PEER_ALLREDUCE")) {
     // Map every rank's partial-sum buffer into every other rank (CUDA IPC over NVLink); the handles
     // travel through the NCCL communicator, so the C ABI needs nothing new. All ranks must take the
     // same decision: a sum of success flags settles it.
-    const size_t qbytes = (size_t)2 * 9 * s->C * sizeof(double);
+    s->peer_slot = (size_t)81 * s->C;
+    const size_t qbytes = 2 * s->peer_slot * sizeof(double);
     const size_t bytes = qbytes + 256;
     double ok = 1.0;
     cudaIpcMemHandle_t mine;
@@ -333,10 +366,22 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     double* d_ok = nullptr;
     TRY(DeviceAlloc(s, &d_ok, 1));
     TRY_CUDA(cudaMemcpy(d_ok, &ok, sizeof(double), cudaMemcpyHostToDevice));
-    TRY(AllReduce(s, d_ok, 1));
+    TRY(NcclAllReduce(s, d_ok, 1));
     TRY_CUDA(cudaStreamSynchronize(s->stream));
     TRY_CUDA(cudaMemcpy(&ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost));
     s->peer_allreduce = (ok == (double)o.world_size);
+  }
+  s->global_dup_pairs = s->num_dup_pairs;
+  if (o.world_size > 1) {
+    // does any rank hold duplicate (point, camera) pairs? (decides whether the cross-term blocks are summed)
+    double dups = (double)s->num_dup_pairs;
+    double* d_dups = nullptr;
+    TRY(DeviceAlloc(s, &d_dups, 1));
+    TRY_CUDA(cudaMemcpy(d_dups, &dups, sizeof(double), cudaMemcpyHostToDevice));
+    TRY(NcclAllReduce(s, d_dups, 1));
+    TRY_CUDA(cudaStreamSynchronize(s->stream));
+    TRY_CUDA(cudaMemcpy(&dups, d_dups, sizeof(double), cudaMemcpyDeviceToHost));
+    s->global_dup_pairs = (long long)dups;
   }
 #undef TRY
 #undef TRY_CUDA

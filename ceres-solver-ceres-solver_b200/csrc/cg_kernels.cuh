@@ -41,7 +41,7 @@ struct CgState {
   int reason;                  // CgReason
   int min_iterations, max_iterations;
   int peer_timeout;            // a peer's partial sum never arrived (cg_step.cuh); fatal
-  unsigned int ticket[4];
+  unsigned int ticket[5];            // [4]: peer_publish_kernel
   unsigned int bar_count, bar_flag;  // grid barrier of cg_step_kernel: arrivals (0 between launches), barriers completed
   double partial[6][kMaxVecBlocks];
 };

@@ -46,7 +46,8 @@ struct CgStepArgs {
   // partial in its own buffer (two slots, alternating) and reads all ranks' in rank order
   int world, rank;
   unsigned int epoch;            // value this launch writes to / expects in the flags
-  double* peer_q[kMaxPeers];     // [rank] -> that rank's buffer: 2 slots x 9C doubles
+  size_t slot_stride;            // doubles between the two slots of a rank's buffer
+  double* peer_q[kMaxPeers];     // [rank] -> that rank's buffer: 2 slots x slot_stride doubles
   unsigned int* peer_flag[kMaxPeers];  // [rank] -> that rank's 2 flags (one per slot, 128 bytes apart)
 };
 
@@ -147,7 +148,7 @@ cg_step_kernel(const CgStepArgs a) {
     if (a.world > 1 && a.q == nullptr) {
       // ---- all-reduce of q over the ranks through peer memory ----
       const int slot = a.epoch & 1u;
-      const size_t n9 = (size_t)9 * a.C;
+      const size_t n9 = a.slot_stride;
       if (on) {
         double* mine = a.peer_q[a.rank] + slot * n9 + o9;
 #pragma unroll
@@ -294,6 +295,65 @@ cg_step_kernel(const CgStepArgs a) {
       a.p[o9 + k] = pk;
       a.x10[o10 + k] = pk;  // S p comes next
     }
+  }
+}
+
+// ----------------------------------------------------------------------------
+// The same exchange for the per-solve sums (reduced rhs, preconditioner blocks):
+// buf[0..n) <- sum over ranks, in rank order, through the peer-mapped buffers.
+// Two plain launches: peer_publish_kernel copies the local partial into this rank's
+// slot and its last CTA releases the epoch flag; peer_sum_kernel waits for every
+// peer's flag and adds the slots up. The kernel boundary orders publish before sum
+// on this GPU; the flags order it across GPUs. Any CTA of the sum kernel can make
+// progress on its own, so no cooperative launch is needed.
+// ----------------------------------------------------------------------------
+struct PeerRefs {
+  int world, rank;
+  unsigned int epoch;
+  size_t slot_stride;
+  double* base[kMaxPeers];
+  unsigned int* flag[kMaxPeers];
+};
+
+__global__ void __launch_bounds__(256)
+peer_publish_kernel(const PeerRefs p, const double* __restrict__ buf, size_t n, CgState* st) {
+  const int slot = p.epoch & 1u;
+  double* mine = p.base[p.rank] + slot * p.slot_stride;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    mine[i] = buf[i];
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int t = atomicAdd(&st->ticket[4], 1u);
+    if (t == gridDim.x - 1) {
+      st->ticket[4] = 0;
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flag[p.rank] + slot * 32), "r"(p.epoch) : "memory");
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+peer_sum_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgState* st) {
+  const int slot = p.epoch & 1u;
+  if (threadIdx.x == 0) {
+    for (int r = 0; r < p.world; ++r) {
+      if (r == p.rank) continue;
+      unsigned int seen;
+      unsigned long long t0, t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[r] + slot * 32) : "memory");
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }
+      } while (seen != p.epoch);
+    }
+  }
+  __syncthreads();
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    double s = 0.0;
+    for (int r = 0; r < p.world; ++r) s += __ldcg(p.base[r] + slot * p.slot_stride + i);  // rank order
+    buf[i] = s;
   }
 }
 

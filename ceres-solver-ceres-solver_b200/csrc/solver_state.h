@@ -88,7 +88,9 @@ struct cb200_solver {
 
   cb200::Nccl nccl;
   // fused all-reduce of the PCG step over NVLink peer memory (cg_step.cuh); null = NCCL path
-  void* d_peer_buf = nullptr;                 // this rank's 2 slots x 9C doubles + 2 flags
+  void* d_peer_buf = nullptr;                 // this rank's 2 slots x peer_slot doubles + 2 flags
+  size_t peer_slot = 0;                       // doubles per slot (81 C: the largest per-solve sum)
+  long long global_dup_pairs = 0;             // duplicate (point, camera) pairs over all ranks
   void* peer_base[16] = {};                   // every rank's buffer as mapped here (own = d_peer_buf)
   unsigned int peer_epoch = 0;
   bool peer_allreduce = false;
