@@ -149,6 +149,7 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-lm", action="store_true", help="skip the device-resident LM loop measurement")
+    ap.add_argument("--no-cusparse", action="store_true", help="skip the cuSPARSE CSR comparison of S*x")
     ap.add_argument("--lm-iterations", type=int, default=10)
     ap.add_argument("--precond", default="schur_jacobi", choices=["schur_jacobi", "spse", "jacobi", "identity"])
     args = ap.parse_args()
@@ -258,6 +259,19 @@ def main():
                 "peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback",
                 "bytes_per_launch": bytes_sx, "ms_per_launch": sx_ms}
 
+    # ---- the reference's CUDA SpMV method (cuSPARSE CSR), re-created: what the fused kernel replaces -------
+    if world == 1 and not args.no_cusparse:
+        try:
+            cs = cusparse_sx(p, values, D)
+            ours = g.isc_multiply(cs["x"])  # same operator, same x: the comparison is like for like
+            roofline["cusparse_csr_reference_method"] = {
+                "sx_ms": cs["sx_ms"], "speedup_of_fused_kernel": cs["sx_ms"] / sx_ms, "method": cs["method"],
+                "rel_diff_of_results": float(np.linalg.norm(ours - cs["y"]) / np.linalg.norm(cs["y"]))}
+            del cs
+            torch.cuda.empty_cache()
+        except Exception as e:  # a comparison, never a reason to lose the bench line
+            roofline["cusparse_csr_reference_method"] = {"unavailable": repr(e)[:200]}
+
     # ---- widened boundary: whole LM iterations on the device-resident problem ----
     lm = None
     if not args.no_lm:
@@ -297,6 +311,53 @@ def main():
         dist.barrier()
         g.close()
         dist.destroy_process_group()
+
+
+def cusparse_sx(p, values, D, iters=10):
+    """SURVEY 8(d) "optional GPU cross-check baseline": S*x the way the reference's own CUDA path would do it --
+    E and F as scalar CSR matrices and one cuSPARSE SpMV per product (CudaSparseMatrix::Right/LeftMultiplyAndAccumulate,
+    cuda_sparse_matrix.cc:185-222, over the CRS views of cuda_partitioned_block_sparse_crs_view.cc:105-119), re-created
+    with torch.sparse CSR (= cusparseSpMV). Library code, a comparison only: nothing of the product runs here. The
+    transposes are stored as their own CSR matrices, which favours this baseline (the reference multiplies with
+    CUSPARSE_OPERATION_TRANSPOSE)."""
+    import torch
+    dev = torch.device("cuda")
+    N, P, C = p.N, p.P, p.C
+    v = torch.from_numpy(values).to(dev)
+    cam = torch.from_numpy(p.cam_idx.astype("int64")).to(dev)
+    pt = torch.repeat_interleave(torch.arange(P, device=dev), torch.from_numpy(np.diff(p.point_row_start).astype("int64")).to(dev))
+    E = torch.sparse_csr_tensor((torch.arange(2 * N + 1, device=dev) * 3).to(torch.int32),
+                                ((pt.repeat_interleave(2) * 3)[:, None] + torch.arange(3, device=dev)[None, :]).reshape(-1).to(torch.int32),
+                                v[:6 * N].clone(), size=(2 * N, 3 * P))
+    F = torch.sparse_csr_tensor((torch.arange(2 * N + 1, device=dev) * 9).to(torch.int32),
+                                ((cam.repeat_interleave(2) * 9)[:, None] + torch.arange(9, device=dev)[None, :]).reshape(-1).to(torch.int32),
+                                v[6 * N:].clone(), size=(2 * N, 9 * C))
+    Et = E.to_sparse_coo().t().coalesce().to_sparse_csr()
+    Ft = F.to_sparse_coo().t().coalesce().to_sparse_csr()
+    # block-diagonal (E'E + D_e^2)^-1 as P dense 3x3 blocks, built with library calls as well
+    e = v[:6 * N].reshape(N, 2, 3)
+    ete = torch.zeros(P, 3, 3, dtype=torch.float64, device=dev).index_add_(0, pt, e.transpose(1, 2) @ e)
+    Dt = torch.from_numpy(D).to(dev)
+    ete += torch.diag_embed(Dt[:3 * P].reshape(P, 3) ** 2)
+    inv = torch.linalg.inv(ete)
+    df2 = Dt[3 * P:] ** 2
+    x = torch.randn(9 * C, dtype=torch.float64, device=dev)
+    def sx():
+        t = F @ x
+        u = Et @ t
+        w = (inv @ u.reshape(P, 3, 1)).reshape(-1)
+        t = t - E @ w
+        return df2 * x + Ft @ t
+    y = sx()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        y = sx()
+    b.record()
+    torch.cuda.synchronize()
+    return {"sx_ms": a.elapsed_time(b) / iters, "x": x.cpu().numpy(), "y": y.cpu().numpy(),
+            "method": "torch.sparse CSR (cusparseSpMV) x4 + batched 3x3 apply; scalar CSR of E, F and their stored transposes"}
 
 
 def cpu_baseline(p, values, residuals, D, precond):
