@@ -318,7 +318,7 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     int coop = 0, per_sm = 0;
     TRY_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, o.device_id));
     TRY_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, cg_step_kernel<kStepNormal, 1>, kStepThreads, 0));
-    const int ctas = Blocks(s->C, kStepThreads);
+    const int ctas = Blocks(s->C, kStepCams);
     s->fused_step_ok = coop != 0 && ctas <= per_sm * s->num_sms && ctas <= kMaxVecBlocks &&
                        !EnvFlag("CB200_NO_FUSED_STEP");
   }

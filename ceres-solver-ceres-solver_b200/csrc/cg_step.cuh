@@ -16,6 +16,7 @@
 namespace cb200 {
 
 constexpr int kStepThreads = 128;
+constexpr int kStepCams = 14;  // cameras per CTA: 9 threads each
 constexpr int kMaxPeers = 16;
 constexpr unsigned long long kPeerTimeoutNs = 4000000000ull;  // a peer rank died or fell out of step
 
@@ -73,7 +74,9 @@ __device__ __forceinline__ void GridBarrier(CgState* st, unsigned int& gen) {
   __syncthreads();
 }
 
-// Block partials -> grid barrier -> every CTA sums all partials in index order.
+// Block partials -> grid barrier -> every CTA sums all partials in the same fixed order
+// (thread t takes partials t, t + 128, ...; then the block tree): deterministic, and
+// identical in every CTA, so all of them take the same decisions.
 // `row0` selects the rows of CgState::partial: the two reductions of one launch
 // use different rows, so a fast CTA cannot overwrite what a slow one still reads.
 template <int K>
@@ -85,22 +88,25 @@ __device__ __forceinline__ void GridSums(CgState* st, unsigned int& gen, int row
     if (threadIdx.x == 0) st->partial[row0 + k][blockIdx.x] = s;
   }
   GridBarrier(st, gen);
-  if (threadIdx.x < K) {
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
     double s = 0.0;
-    const volatile double* part = st->partial[row0 + threadIdx.x];
-    for (unsigned int b = 0; b < gridDim.x; ++b) s += part[b];
-    sums[threadIdx.x] = s;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) s += __ldcg(&st->partial[row0 + k][b]);
+    sums[k] = BlockSum(s, sbuf);
   }
-  __syncthreads();
 }
 
+// One thread per scalar entry: a CTA owns kStepCams cameras (9 threads each, 2 idle).
+// Everything is coalesced: vectors at 9*camera + i, accumulators at 10*camera + i,
+// preconditioner rows at 81*camera + 9*i.
 template <int KIND, int PRECOND>
 __global__ void __launch_bounds__(kStepThreads)
 cg_step_kernel(const CgStepArgs a) {
   CgState* st = a.st;
   if (st->done || st->peer_timeout) return;
   __shared__ double sbuf[8];
-  __shared__ double sums[4];
+  __shared__ double sR[kStepThreads];
+  double sums[3];
   // scalars of the iteration, read before anything is written (CTA 0 writes after barrier 1)
   const int it = st->iter;
   double rho = st->rho;
@@ -109,64 +115,45 @@ cg_step_kernel(const CgStepArgs a) {
   const int min_it = st->min_iterations, max_it = st->max_iterations;
   unsigned int gen = *reinterpret_cast<volatile unsigned int*>(&st->bar_flag);
   const bool writer = blockIdx.x == 0 && threadIdx.x == 0;
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool on = c < a.C;
-  const size_t o9 = (size_t)c * 9, o10 = (size_t)c * 10;
+  const int local = threadIdx.x / 9;             // camera within the CTA
+  const int i = threadIdx.x - 9 * local;         // entry within the camera
+  const int c = blockIdx.x * kStepCams + local;
+  const bool on = local < kStepCams && c < a.C;
+  const size_t o9 = (size_t)c * 9 + i, o10 = (size_t)c * 10 + i;
 
-  double p[9], q[9], x[9], r[9], z[9];
-#pragma unroll
-  for (int k = 0; k < 9; ++k) { p[k] = 0.0; q[k] = 0.0; x[k] = 0.0; r[k] = 0.0; z[k] = 0.0; }
+  double p = 0.0, q = 0.0, x = 0.0, r = 0.0, z = 0.0;
   double alpha = 0.0;
 
   if (KIND != kStepStart) {
     // ---- fold the accumulators: q = F'(..) of the multiplied vector ----
     if (on) {
-#pragma unroll
-      for (int k = 0; k < 9; ++k) { p[k] = a.p[o9 + k]; x[k] = a.x[o9 + k]; }
+      p = a.p[o9];
+      x = a.x[o9];
       if (a.q != nullptr) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) q[k] = a.q[o9 + k];
+        q = a.q[o9];
       } else {
-        // all loads first (independent, pipelined), the zeroing stores afterwards:
-        // interleaving them serialises one L2 round trip per element
-        for (int rep = 0; rep < a.nrep; ++rep) {
-          const double* y = a.yrep + (size_t)rep * a.rep_stride + o10;
-#pragma unroll
-          for (int k = 0; k < 5; ++k) {
-            const double2 v = __ldcg(reinterpret_cast<const double2*>(y) + k);
-            q[2 * k] += v.x;
-            if (k < 4) q[2 * k + 1] += v.y;
-          }
-        }
-        for (int rep = 0; rep < a.nrep; ++rep) {
-          double2* y = reinterpret_cast<double2*>(a.yrep + (size_t)rep * a.rep_stride + o10);
-#pragma unroll
-          for (int k = 0; k < 5; ++k) y[k] = make_double2(0.0, 0.0);
-        }
+        // all loads first (independent, pipelined), the zeroing stores afterwards
+        for (int rep = 0; rep < a.nrep; ++rep) q += __ldcg(a.yrep + (size_t)rep * a.rep_stride + o10);
+        for (int rep = 0; rep < a.nrep; ++rep) a.yrep[(size_t)rep * a.rep_stride + o10] = 0.0;
       }
     }
     if (a.world > 1 && a.q == nullptr) {
       // ---- all-reduce of q over the ranks through peer memory ----
       const int slot = a.epoch & 1u;
-      const size_t n9 = a.slot_stride;
-      if (on) {
-        double* mine = a.peer_q[a.rank] + slot * n9 + o9;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) mine[k] = q[k];
-      }
+      if (on) a.peer_q[a.rank][slot * a.slot_stride + o9] = q;
       GridBarrier(st, gen);  // every CTA of this rank has published
       if (threadIdx.x == 0) {
         if (blockIdx.x == 0) {
           __threadfence_system();
           asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(a.epoch) : "memory");
         }
-        for (int r = 0; r < a.world; ++r) {
-          if (r == a.rank) continue;
+        for (int rk = 0; rk < a.world; ++rk) {
+          if (rk == a.rank) continue;
           unsigned int seen;
           unsigned long long t0, t1;
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
           do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[r] + slot * 32) : "memory");
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[rk] + slot * 32) : "memory");
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
             if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }  // never hang the GPU
           } while (seen != a.epoch);
@@ -174,28 +161,17 @@ cg_step_kernel(const CgStepArgs a) {
       }
       __syncthreads();
       if (on) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) q[k] = 0.0;
-        for (int r = 0; r < a.world; ++r) {  // rank order: the same sum, bit for bit, on every rank
-          const double* theirs = a.peer_q[r] + slot * n9 + o9;
-#pragma unroll
-          for (int k = 0; k < 9; ++k) q[k] += __ldcg(theirs + k);
-        }
+        q = 0.0;
+        for (int rk = 0; rk < a.world; ++rk)  // rank order: the same sum, bit for bit, on every rank
+          q += __ldcg(a.peer_q[rk] + slot * a.slot_stride + o9);
       }
     }
-    if (on) {
-      // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
-      if (a.Df != nullptr) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) { const double d = a.Df[o9 + k]; q[k] += d * d * (KIND == kStepResetB ? x[k] : p[k]); }
-      }
-    }
+    // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
+    if (on && a.Df != nullptr) { const double d = a.Df[o9]; q += d * d * (KIND == kStepResetB ? x : p); }
   }
   if (KIND == kStepNormal || KIND == kStepResetA) {
     // ---- pq, alpha (:190-214) ----
-    double v[3] = {0.0, 0.0, 0.0};
-#pragma unroll
-    for (int k = 0; k < 9; ++k) { v[0] += p[k] * q[k]; v[1] += p[k] * p[k]; v[2] += q[k] * q[k]; }
+    const double v[3] = {p * q, p * p, q * q};
     GridSums<3>(st, gen, 0, v, sums, sbuf);
     const double pq = sums[0];
     if (pq <= 0.0 || isinf(pq)) {
@@ -213,46 +189,37 @@ cg_step_kernel(const CgStepArgs a) {
     }
     // ---- x += alpha p (:216) ----
     if (on) {
-#pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        x[k] += alpha * p[k];
-        a.x[o9 + k] = x[k];
-        if (a.trace != nullptr && it <= a.max_trace) a.trace[(size_t)(it - 1) * 9 * a.C + o9 + k] = x[k];
-        if (KIND == kStepResetA) a.x10[o10 + k] = x[k];  // S x comes next
-      }
+      x += alpha * p;
+      a.x[o9] = x;
+      if (a.trace != nullptr && it <= a.max_trace) a.trace[(size_t)(it - 1) * 9 * a.C + o9] = x;
+      if (KIND == kStepResetA) a.x10[o10] = x;  // S x comes next
     }
     if (KIND == kStepResetA) return;
   }
   // ---- residual (:221-227) ----
   if (on) {
+    if (KIND == kStepNormal) r = a.r[o9] - alpha * q;
+    else if (KIND == kStepResetB) r = a.rhs[o9] - q;
+    else r = a.r[o9];
+    if (KIND != kStepStart) a.r[o9] = r;
+  }
+  // ---- z = M^-1 r (:160-161): row i of the camera's block times the camera's r ----
+  if (PRECOND == 0) {
+    z = r;
+  } else {
+    sR[threadIdx.x] = r;
+    __syncthreads();
+    if (on) {
+      const double* B = a.blocks + (size_t)c * 81 + 9 * i;
+      const double* rc = sR + 9 * local;
+      double s = 0.0;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      if (KIND == kStepNormal) r[k] = a.r[o9 + k] - alpha * q[k];
-      else if (KIND == kStepResetB) r[k] = a.rhs[o9 + k] - q[k];
-      else r[k] = a.r[o9 + k];
-      if (KIND != kStepStart) a.r[o9 + k] = r[k];
-    }
-    // ---- z = M^-1 r (:160-161) ----
-    if (PRECOND == 0) {
-#pragma unroll
-      for (int k = 0; k < 9; ++k) z[k] = r[k];
-    } else {
-      const double* B = a.blocks + (size_t)c * 81;
-#pragma unroll
-      for (int i = 0; i < 9; ++i) {
-        double s = 0.0;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) s += __ldg(B + i * 9 + k) * r[k];
-        z[i] = s;
-      }
+      for (int k = 0; k < 9; ++k) s += __ldg(B + k) * rc[k];
+      z = s;
     }
   }
-  double v[3] = {0.0, 0.0, 0.0};
-#pragma unroll
-  for (int k = 0; k < 9; ++k) {
-    v[0] += r[k] * z[k];
-    if (KIND != kStepStart && on) { v[1] += x[k] * (a.rhs[o9 + k] + r[k]); v[2] += r[k] * r[k]; }
-  }
+  double v[3] = {r * z, 0.0, 0.0};
+  if (KIND != kStepStart && on) { v[1] = x * (a.rhs[o9] + r); v[2] = r * r; }
   GridSums<3>(st, gen, 3, v, sums, sbuf);
   int next_it = it;
   if (KIND != kStepStart) {
@@ -289,14 +256,15 @@ cg_step_kernel(const CgStepArgs a) {
   }
   if (fail) return;
   if (on) {
-#pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      const double pk = (next_it == 1) ? z[k] : z[k] + beta * p[k];
-      a.p[o9 + k] = pk;
-      a.x10[o10 + k] = pk;  // S p comes next
-    }
+    const double pk = (next_it == 1) ? z : z + beta * p;
+    a.p[o9] = pk;
+    a.x10[o10] = pk;  // S p comes next
   }
 }
+
+}  // namespace cb200
+
+namespace cb200 {
 
 // ----------------------------------------------------------------------------
 // The same exchange for the per-solve sums (reduced rhs, preconditioner blocks):
