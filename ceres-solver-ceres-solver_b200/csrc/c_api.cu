@@ -148,9 +148,29 @@ void cb200_destroy(cb200_solver* s) {
   if (!s) return;
   if (s->opt.device_id >= 0) cudaSetDevice(s->opt.device_id);
   if (s->stream) cudaStreamSynchronize(s->stream);
-  for (int r = 0; r < 16; ++r)
+  bool release_peer_memory = true;
+  if (s->peer_allreduce && s->h_cg && !s->h_cg->peer_timeout && s->d_cg) {
+    // All ranks leave together: no rank unmaps or frees a buffer that a slower peer may still be
+    // summing. One NCCL all-reduce is the rendezvous (it completes here only after every rank has
+    // reached it, i.e. is past all its peer reads). If a peer never shows up, give up after a few
+    // seconds and leak the buffers rather than free memory somebody may still read.
+    release_peer_memory = false;
+    double* scratch = &s->d_cg->partial[5][0];
+    if (s->nccl.AllReduce(scratch, scratch, 1, /*ncclDouble*/ 8, /*ncclSum*/ 0, s->nccl.comm, s->stream) == 0) {
+      const auto t0 = std::chrono::steady_clock::now();
+      while (std::chrono::steady_clock::now() - t0 < std::chrono::seconds(5)) {
+        if (cudaStreamQuery(s->stream) != cudaErrorNotReady) { release_peer_memory = true; break; }
+      }
+    }
+    if (!release_peer_memory) {
+      cudaGetLastError();
+      delete s;  // the stream still holds the pending collective: leave everything else to process exit
+      return;
+    }
+  }
+  for (int r = 0; r < 16 && release_peer_memory; ++r)
     if (s->peer_base[r] && s->peer_base[r] != s->d_peer_buf) cudaIpcCloseMemHandle(s->peer_base[r]);
-  if (s->d_peer_buf) cudaFree(s->d_peer_buf);
+  if (s->d_peer_buf && release_peer_memory) cudaFree(s->d_peer_buf);
   if (s->nccl.comm && s->nccl.CommDestroy) s->nccl.CommDestroy(s->nccl.comm);
   for (void* p : s->allocations) cudaFree(p);
   if (s->h_cg) cudaFreeHost(s->h_cg);
