@@ -79,21 +79,43 @@ __device__ __forceinline__ void GridBarrier(CgState* st, unsigned int& gen) {
 // identical in every CTA, so all of them take the same decisions.
 // `row0` selects the rows of CgState::partial: the two reductions of one launch
 // use different rows, so a fast CTA cannot overwrite what a slow one still reads.
+// K block-wide sums in one pass (fixed tree => deterministic); result valid in every thread.
+template <int K>
+__device__ __forceinline__ void BlockSums(double* v, double* sbuf /* >= 4 * K */) {
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], off);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) sbuf[4 * k + warp] = v[k];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < K; ++k) v[k] = (sbuf[4 * k] + sbuf[4 * k + 1]) + (sbuf[4 * k + 2] + sbuf[4 * k + 3]);
+}
+
 template <int K>
 __device__ __forceinline__ void GridSums(CgState* st, unsigned int& gen, int row0, const double* vals,
                                          double* sums, double* sbuf) {
+  double v[K];
 #pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const double s = BlockSum(vals[k], sbuf);
-    if (threadIdx.x == 0) st->partial[row0 + k][blockIdx.x] = s;
-  }
+  for (int k = 0; k < K; ++k) v[k] = vals[k];
+  BlockSums<K>(v, sbuf);
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+    if (threadIdx.x == k) st->partial[row0 + k][blockIdx.x] = v[k];
   GridBarrier(st, gen);
 #pragma unroll
   for (int k = 0; k < K; ++k) {
     double s = 0.0;
     for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x) s += __ldcg(&st->partial[row0 + k][b]);
-    sums[k] = BlockSum(s, sbuf);
+    sums[k] = s;
   }
+  BlockSums<K>(sums, sbuf);
 }
 
 // One thread per scalar entry: a CTA owns kStepCams cameras (9 threads each, 2 idle).
@@ -104,7 +126,7 @@ __global__ void __launch_bounds__(kStepThreads)
 cg_step_kernel(const CgStepArgs a) {
   CgState* st = a.st;
   if (st->done || st->peer_timeout) return;
-  __shared__ double sbuf[8];
+  __shared__ double sbuf[12];
   __shared__ double sR[kStepThreads];
   double sums[3];
   // scalars of the iteration, read before anything is written (CTA 0 writes after barrier 1)
@@ -123,6 +145,22 @@ cg_step_kernel(const CgStepArgs a) {
 
   double p = 0.0, q = 0.0, x = 0.0, r = 0.0, z = 0.0;
   double alpha = 0.0;
+  // everything this thread reads from global memory is requested up front: the loads are in flight
+  // together instead of one L2 round trip after each grid barrier
+  double r_old = 0.0, rhs_i = 0.0, df = 0.0;
+  double Brow[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) Brow[k] = 0.0;
+  if (on) {
+    r_old = a.r[o9];
+    rhs_i = a.rhs[o9];
+    if (a.Df != nullptr) df = a.Df[o9];
+    if (PRECOND != 0) {
+      const double* B = a.blocks + (size_t)c * 81 + 9 * i;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) Brow[k] = __ldg(B + k);
+    }
+  }
 
   if (KIND != kStepStart) {
     // ---- fold the accumulators: q = F'(..) of the multiplied vector ----
@@ -167,7 +205,7 @@ cg_step_kernel(const CgStepArgs a) {
       }
     }
     // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
-    if (on && a.Df != nullptr) { const double d = a.Df[o9]; q += d * d * (KIND == kStepResetB ? x : p); }
+    if (on) q += df * df * (KIND == kStepResetB ? x : p);
   }
   if (KIND == kStepNormal || KIND == kStepResetA) {
     // ---- pq, alpha (:190-214) ----
@@ -198,9 +236,9 @@ cg_step_kernel(const CgStepArgs a) {
   }
   // ---- residual (:221-227) ----
   if (on) {
-    if (KIND == kStepNormal) r = a.r[o9] - alpha * q;
-    else if (KIND == kStepResetB) r = a.rhs[o9] - q;
-    else r = a.r[o9];
+    if (KIND == kStepNormal) r = r_old - alpha * q;
+    else if (KIND == kStepResetB) r = rhs_i - q;
+    else r = r_old;
     if (KIND != kStepStart) a.r[o9] = r;
   }
   // ---- z = M^-1 r (:160-161): row i of the camera's block times the camera's r ----
@@ -210,16 +248,15 @@ cg_step_kernel(const CgStepArgs a) {
     sR[threadIdx.x] = r;
     __syncthreads();
     if (on) {
-      const double* B = a.blocks + (size_t)c * 81 + 9 * i;
       const double* rc = sR + 9 * local;
       double s = 0.0;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) s += __ldg(B + k) * rc[k];
+      for (int k = 0; k < 9; ++k) s += Brow[k] * rc[k];
       z = s;
     }
   }
   double v[3] = {r * z, 0.0, 0.0};
-  if (KIND != kStepStart && on) { v[1] = x * (a.rhs[o9] + r); v[2] = r * r; }
+  if (KIND != kStepStart && on) { v[1] = x * (rhs_i + r); v[2] = r * r; }
   GridSums<3>(st, gen, 3, v, sums, sbuf);
   int next_it = it;
   if (KIND != kStepStart) {
