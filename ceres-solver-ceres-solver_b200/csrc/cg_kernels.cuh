@@ -186,8 +186,9 @@ __global__ void reduce_replicas_kernel(const int* done, double* __restrict__ yre
 
 // x [9C] -> x10 [10C]: camera vectors are gathered with 16-byte loads, which need
 // 16-byte aligned 9-vectors (the 10th double is never read as data).
-__global__ void pad10_kernel(const int* done, const double* __restrict__ x, double* __restrict__ x10, int n) {
-  if (done != nullptr && *done) return;
+__global__ void pad10_kernel(const int* done, int run_when_done, const double* __restrict__ x,
+                             double* __restrict__ x10, int n) {
+  if (done != nullptr && ((*done != 0) != (run_when_done != 0))) return;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) x10[i + i / 9] = x[i];
 }

@@ -56,7 +56,8 @@ struct StreamArgs {
   int nrep;
   int rep_stride;
   double* y_e;              // [3P] (kModeBack)
-  const int* done;          // device convergence flag; the kernel is a no-op when set
+  const int* done;          // device convergence flag (or null): the kernel is a no-op when it is set ...
+  int run_when_done;        // ... or, if this is non-zero, when it is NOT set (speculative back substitution)
   double* model;            // (kModeBack) or null: accumulates sum_rows m.(b - m/2) with m = E y_e + F x, the
                             // model cost change of the step -y (trust_region_minimizer.cc:430-438)
 };
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(kStreamThreads, 3)
 point_stream_kernel(const StreamArgs a) {
   using L = StreamLayout<MODE, BUILD>;
   static_assert(!BUILD || MODE == kModeRhs, "the E'E build rides on the rhs pass");
-  if (a.done != nullptr && *a.done != 0) return;
+  if (a.done != nullptr && ((*a.done != 0) != (a.run_when_done != 0))) return;
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -431,7 +432,7 @@ template <int MODE, bool BUILD>
 __global__ void __launch_bounds__(256)
 point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
                   const int* __restrict__ row_start, const int* __restrict__ cam) {
-  if (a.done != nullptr && *a.done != 0) return;
+  if (a.done != nullptr && ((*a.done != 0) != (a.run_when_done != 0))) return;
   __shared__ double sbuf[8];
   const int p = long_points[blockIdx.x];
   const int r0 = row_start[p], r1 = row_start[p + 1];
