@@ -177,6 +177,9 @@ void cb200_destroy(cb200_solver* s) {
   if (s->h_lm_scalars) cudaFreeHost(s->h_lm_scalars);
   for (auto& e : s->ev)
     if (e) cudaEventDestroy(e);
+  if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+  if (s->ev_join) cudaEventDestroy(s->ev_join);
+  if (s->side_stream) cudaStreamDestroy(s->side_stream);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
 }
@@ -229,6 +232,9 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
 
   TRY_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   for (auto& e : s->ev) TRY_CUDA(cudaEventCreate(&e));
+  TRY_CUDA(cudaStreamCreateWithFlags(&s->side_stream, cudaStreamNonBlocking));
+  TRY_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+  TRY_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
 
   // local structure arrays
   std::vector<int> row_start(s->P_loc + 1), cam(s->N_loc);

@@ -47,6 +47,9 @@ struct cb200_solver {
 
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[8] = {};
+  // camera-sized start-up work of a solve runs beside the preconditioner build (single GPU)
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 
   // device: structure
   int *d_cam = nullptr, *d_row_start = nullptr, *d_long_points = nullptr, *d_empty_points = nullptr;
