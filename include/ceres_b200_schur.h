@@ -207,7 +207,9 @@ int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
 /* Device-resident timing of one op (CUDA events on the solver's stream, `iters`
  * back-to-back launches after `warmup`); ms_out = average per launch.
  * op: 0 S*x (isc multiply), 1 EtE inverse build, 2 rhs, 3 Schur-Jacobi build,
- * 4 back substitute, 5 one PCG iteration (fixed work, no convergence test). */
+ * 4 back substitute, 6 the fused S*x kernel alone; the separate products that the
+ * reference's evaluation_benchmark.cc times (:333-491): 7 / 8 Right / Left E,
+ * 9 / 10 Right / Left F, 11 UpdateBlockDiagonalFtF, 12 PSE preconditioner apply. */
 int cb200_time_op(cb200_solver* s, int op, int warmup, int iters, float* ms_out,
                   int* launches_out);
 
