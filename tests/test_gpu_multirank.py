@@ -61,3 +61,54 @@ def test_two_gpu_solve_matches_oracle(ptype):
         assert np.all(np.isnan(x[:ne][mask]))
         covered[pb:pe] = True
     assert covered.all()
+
+
+def _lm_worker(rank, world, uid, out):
+    m = util.pkg()
+    p = m.SyntheticBAL(31, 3000, 14000, seed=7, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    g = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=500,
+                                         device_id=rank, rank=rank, world_size=world, nccl_unique_id=uid)
+    g.bal_attach(p.observations)
+    g.bal_set_parameters(p.cameras, p.points)
+    r = g.lm_minimize(eta=1e-2, max_num_iterations=6)
+    cam, pts = g.bal_get_parameters()
+    out[rank] = (r["initial_cost"], r["final_cost"], [(i["iteration"], i["linear_solver_iterations"], i["cost"])
+                                                      for i in r["iterations"]], cam, pts, g.point_begin, g.point_end)
+    g.close()
+
+
+def test_two_gpu_lm_loop_matches_reference_loop():
+    """The device trust-region loop with the points sharded over two GPUs (evaluator, column norms,
+    gradient, candidate cost and model cost all reduced over ranks) against the CPU loop."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from oracle import binding as ob
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    world = 2
+    uid = m.nccl_unique_id()
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    procs = [ctx.Process(target=_lm_worker, args=(r, world, uid, out)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    for pr in procs:
+        pr.join(300)
+        assert pr.exitcode == 0
+    p = m.SyntheticBAL(31, 3000, 14000, seed=7, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    o = ob.Oracle(util.oracle_structure(p.structure), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI,
+                  max_num_iterations=500)
+    want = lmr.minimize(p, p.cameras, p.points, lambda v, r, D, e: o.solve(v, r, D, e, -1.0), eta=1e-2,
+                        max_num_iterations=6)
+    pts_all = np.full(3 * p.P, np.nan)
+    for r in range(world):
+        initial, final, its, cam, pts, pb, pe = out[r]
+        assert abs(initial - want["initial_cost"]) <= 1e-12 * want["initial_cost"]
+        assert abs(final - want["final_cost"]) <= 1e-8 * want["final_cost"]
+        assert len(its) == len(want["iterations"])
+        for (it, ls, cost), b in zip(its, want["iterations"]):
+            assert it == b["iteration"] and ls == b["linear_solver_iterations"]
+            assert abs(cost - b["cost"]) <= 1e-8 * b["cost"]
+        assert util.rel_err(cam, want["cameras"]) < 1e-7
+        pts_all[3 * pb:3 * pe] = pts[3 * pb:3 * pe]
+    assert util.rel_err(pts_all, want["points"]) < 1e-7
