@@ -183,6 +183,39 @@ def test_duplicate_and_long_points():
     compare_solve(m, st, values, b, D, "SCHUR_POWER_SERIES_EXPANSION", r_tol=1e-6, max_it=30)
 
 
+def test_ragged_tracks_single_row_and_empty_points():
+    """Track lengths the tile planner has to cope with: many single-row points (a tile holds at most 16
+    points, flatten.h kTilePoints), points without any row (legal in the block structure) scattered
+    between them, and a few long ones. Unit ops and a full solve against the oracle."""
+    m = util.pkg()
+    rng = np.random.default_rng(21)
+    C, P = 40, 3000
+    lens = rng.choice([0, 1, 1, 1, 2, 3, 5, 17, 31, 32], size=P, p=[.08, .3, .15, .1, .15, .1, .06, .03, .02, .01])
+    lens[:40] = 1  # a run of single-row points: the 16-point cap binds
+    lens[40:60] = 0  # a run of empty points inside the shard
+    lens[-1] = 0
+    prs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    cam = np.concatenate([np.sort(rng.choice(C, size=L, replace=False)) for L in lens if L > 0]).astype(np.int32)
+    st = m.BlockStructure.bal(prs, cam, C)
+    N = len(cam)
+    values, b = rng.standard_normal(24 * N), rng.standard_normal(2 * N)
+    D = np.abs(rng.standard_normal(3 * P + 9 * C)) + 0.5  # empty points need D_e != 0: (E'E + D^2) = D^2
+    o = ob.Oracle(util.oracle_structure(st), num_threads=4, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=100)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=100)
+    g.upload(values, b, D)
+    g.isc_init()
+    o.isc_init(values, D, b)
+    assert util.rel_err(g.ete_inverse(), o.ete_inverse()) < OP_TOL
+    assert util.rel_err(g.isc_rhs(), o.isc_rhs()) < OP_TOL
+    x = rng.standard_normal(9 * C)
+    assert util.rel_err(g.isc_multiply(x), o.isc_multiply(x)) < OP_TOL
+    assert util.rel_err(g.isc_back_substitute(x), o.isc_back_substitute(x)) < OP_TOL
+    assert util.rel_err(g.schur_jacobi(invert=False), o.schur_jacobi(values, D, invert=False)) < OP_TOL
+    g.close()
+    compare_solve(m, st, values, b, D, "SCHUR_JACOBI", r_tol=1e-9)
+    compare_solve(m, st, values, b, D, "JACOBI", r_tol=1e-9)
+
+
 @pytest.mark.parametrize("ptype", ["SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION"])
 def test_lm_shaped_solve_ladybug_scale(ptype):
     """Snavely Jacobian, Jacobi scaling, D from the LM strategy, eta = 1e-2 (bundle_adjuster.cc:114)."""
