@@ -122,6 +122,8 @@ SYMBOLS = {
     "cb200_bal_get_parameters": (ctypes.c_int, [_H, _dp, _dp]),
     "cb200_bal_evaluate": (ctypes.c_int, [_H, ctypes.c_int, _dp, _dp]),
     "cb200_download_jacobian": (ctypes.c_int, [_H, _dp, _dp]),
+    "cb200_host_register": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_size_t]),
+    "cb200_host_unregister": (ctypes.c_int, [ctypes.c_void_p]),
     "cb200_lm_minimize": (ctypes.c_int, [_H, ctypes.POINTER(CLmOptions), ctypes.POINTER(CLmSummary),
                                          ctypes.POINTER(CLmIteration), ctypes.c_int]),
 }
@@ -146,6 +148,15 @@ def lib():
 
 class B200Error(RuntimeError):
     pass
+
+
+def host_register(array):
+    """Page-lock a numpy array in place (cb200_host_register): uploads from it then run at PCIe rate."""
+    _check(lib().cb200_host_register(array.ctypes.data, array.nbytes))
+
+
+def host_unregister(array):
+    _check(lib().cb200_host_unregister(array.ctypes.data))
 
 
 def _check(rc):

@@ -14,6 +14,8 @@
 #ifndef CERES_B200_SCHUR_H_
 #define CERES_B200_SCHUR_H_
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -124,6 +126,15 @@ void cb200_destroy(cb200_solver* s);
  * block_sparse_matrix.cc:58-67). Both outputs have world_size + 1 entries. */
 int cb200_shard_plan(const cb200_structure* structure, int num_eliminate_blocks, int world_size,
                      int* point_bounds, int* row_bounds);
+
+/* Page-lock a caller-owned host buffer (cudaHostRegister) so that cb200_solve /
+ * cb200_upload copy from it at full PCIe rate instead of through the driver's
+ * staging buffer. Meant for BlockSparseMatrix::values(), whose address is stable
+ * for the life of a Solve(); the reference's own switch for this is
+ * BlockSparseMatrix(..., use_page_locked_memory) (block_sparse_matrix.cc:178-180,
+ * 810-826). Registering a buffer twice is not an error. */
+int cb200_host_register(const void* ptr, size_t bytes);
+int cb200_host_unregister(const void* ptr);
 
 /* sizes: num_cols = 3P + 9C (x), num_cols_f = 9C, num_rows = 2N. */
 int cb200_num_rows(const cb200_solver* s);

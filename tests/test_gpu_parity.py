@@ -386,3 +386,24 @@ def test_bundle_adjuster_cli_matches_reference_loop(tmp_path):
     c_out, _, _ = out.problem().evaluate(jacobian=False)
     assert abs(c_out - want["final_cost"]) <= 1e-8 * want["final_cost"]
     assert open(tmp_path / "out.ply").readline().strip() == "ply"
+
+
+def test_host_registered_buffers_upload_faster_and_solve_the_same():
+    """cb200_host_register (what the adapter does to BlockSparseMatrix::values()): the same solve from a
+    page-locked numpy buffer, with the H2D copy at least as fast as from pageable memory."""
+    m = util.pkg()
+    p = m.SyntheticBAL.named("ladybug")
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    g = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=100)
+    x0, s0 = g.solve(values, residuals, D, 1e-2, -1.0)
+    x0, s0 = g.solve(values, residuals, D, 1e-2, -1.0)  # (second call: first-touch effects gone)
+    m.host_register(values)
+    m.host_register(values)  # twice is not an error
+    try:
+        x1, s1 = g.solve(values, residuals, D, 1e-2, -1.0)
+        x1, s1 = g.solve(values, residuals, D, 1e-2, -1.0)
+    finally:
+        m.host_unregister(values)
+    assert s1["num_iterations"] == s0["num_iterations"] and util.rel_err(x1, x0) < 1e-11  # (atomics: not bitwise)
+    assert s1["h2d_ms"] <= 1.05 * s0["h2d_ms"], (s0["h2d_ms"], s1["h2d_ms"])
+    g.close()
