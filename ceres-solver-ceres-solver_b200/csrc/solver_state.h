@@ -97,6 +97,7 @@ struct cb200_solver {
   void* peer_base[16] = {};                   // every rank's buffer as mapped here (own = d_peer_buf)
   unsigned int peer_epoch = 0;
   bool peer_allreduce = false;
+  int stream_ctas_per_sm[4][2] = {};          // occupancy of point_stream_kernel<MODE, BUILD>, filled on first use
   int launches = 0;
   std::vector<void*> allocations;
 };
