@@ -13,7 +13,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SRC = ["c_api.cc", "small_blas.h", "block_structure.h", "partitioned_view.h",
-        "implicit_schur.h", "schur_jacobi.h", "solver.h"]
+        "implicit_schur.h", "schur_jacobi.h", "solver.h", "explicit_schur.h"]
 
 IDENTITY, JACOBI, SCHUR_JACOBI, SCHUR_POWER_SERIES_EXPANSION = 0, 1, 2, 3
 TERMINATION = {0: "SUCCESS", 1: "NO_CONVERGENCE", 2: "FAILURE", 3: "FATAL_ERROR"}
@@ -76,6 +76,12 @@ def lib(native=False):
                                ctypes.c_double, dp, ctypes.POINTER(OracleSummary),
                                dp, ctypes.c_int]
     L.oracle_reduced_solution.argtypes = [ctypes.c_void_p, dp]
+    L.oracle_explicit_eliminate.argtypes = [ctypes.c_void_p, dp, dp, dp, ip, ip, ip, ip, ip,
+                                            ip, dp, dp]
+    L.oracle_explicit_multiply.argtypes = [ctypes.c_void_p, dp, dp]
+    L.oracle_explicit_solve.argtypes = [ctypes.c_void_p, dp, dp, dp, ctypes.c_double,
+                                        ctypes.c_double, dp, ctypes.POINTER(OracleSummary),
+                                        dp, ctypes.c_int]
     L.oracle_cg_dense.argtypes = [ctypes.c_int, dp, dp, dp, ctypes.c_int,
                                   ctypes.c_int, ctypes.c_int, ctypes.c_double,
                                   ctypes.c_double, ctypes.POINTER(OracleSummary)]
@@ -212,6 +218,40 @@ class Oracle:
         self.L.oracle_solve(self.h, _dp(values), _dp(b), _dp(D), q_tolerance,
                             r_tolerance, _dp(x), ctypes.byref(s), _dp(trace),
                             max_trace)
+        summary = {"num_iterations": s.num_iterations,
+                   "termination_type": s.termination_type,
+                   "message": s.message.decode()}
+        if max_trace:
+            summary["trace"] = trace[:min(max_trace, max(s.num_iterations, 0))]
+        return x, summary
+
+    # -- use_explicit_schur_complement = true (oracle/explicit_schur.h) --
+    def explicit_eliminate(self, values, b, D):
+        """Block CRS (upper triangle) of the explicit Schur complement + reduced rhs."""
+        nb, nc, nv = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        self.L.oracle_explicit_eliminate(self.h, _dp(values), _dp(b), _dp(D), ctypes.byref(nb),
+                                         ctypes.byref(nc), ctypes.byref(nv), None, None, None,
+                                         None, None)
+        row_ptr = np.zeros(nb.value + 1, dtype=np.int32)
+        cols = np.zeros(nc.value, dtype=np.int32)
+        pos = np.zeros(nc.value, dtype=np.int32)
+        vals = np.zeros(nv.value)
+        rhs = np.zeros(self.st.num_cols_f)
+        self.L.oracle_explicit_eliminate(self.h, _dp(values), _dp(b), _dp(D), None, None, None,
+                                         _ip(row_ptr), _ip(cols), _ip(pos), _dp(vals), _dp(rhs))
+        return row_ptr, cols, pos, vals, rhs
+
+    def explicit_multiply(self, x):
+        y = np.zeros(self.st.num_cols_f)
+        self.L.oracle_explicit_multiply(self.h, _dp(x), _dp(y))
+        return y
+
+    def explicit_solve(self, values, b, D, q_tolerance=0.0, r_tolerance=0.0, max_trace=0):
+        x = np.zeros(self.st.num_cols)
+        s = OracleSummary()
+        trace = np.zeros((max_trace, self.st.num_cols_f)) if max_trace else None
+        self.L.oracle_explicit_solve(self.h, _dp(values), _dp(b), _dp(D), q_tolerance,
+                                     r_tolerance, _dp(x), ctypes.byref(s), _dp(trace), max_trace)
         summary = {"num_iterations": s.num_iterations,
                    "termination_type": s.termination_type,
                    "message": s.message.decode()}

@@ -9,6 +9,7 @@
 #include <chrono>
 #include <cstring>
 
+#include "explicit_schur.h"
 #include "solver.h"
 
 using namespace oracle;
@@ -20,6 +21,7 @@ struct OracleHandle {
   std::unique_ptr<IterativeSchurComplementSolver> solver;
   std::unique_ptr<ImplicitSchurComplement> isc;  // stand-alone operator tests
   std::unique_ptr<SchurJacobiPreconditioner> sj;
+  std::unique_ptr<ExplicitSchurComplementSolver> explicit_solver;  // use_explicit_schur_complement
   std::string message;
 };
 
@@ -180,6 +182,59 @@ int oracle_reduced_solution(OracleHandle* h, double* out) {
   const Vec& v = h->solver->reduced_solution();
   if (out) std::memcpy(out, v.data(), sizeof(double) * v.size());
   return (int)v.size();
+}
+
+// ---- use_explicit_schur_complement = true (explicit_schur.h) ----------------
+static ExplicitSchurComplementSolver* ExplicitSolver(OracleHandle* h) {
+  if (!h->explicit_solver)
+    h->explicit_solver = std::make_unique<ExplicitSchurComplementSolver>(&h->bs, h->options);
+  return h->explicit_solver.get();
+}
+
+// InitStorage + SchurEliminator::Eliminate. Sizes come back through the three
+// counters; a second call with the arrays non-NULL fills them: block CRS of the
+// upper triangle (row_ptr: num_blocks + 1, cols / positions: num_cells), the
+// values and the reduced right hand side.
+void oracle_explicit_eliminate(OracleHandle* h, const double* values, const double* b,
+                               const double* D, int* num_blocks, int* num_cells,
+                               int* num_values, int* row_ptr, int* cols, int* positions,
+                               double* lhs_values, double* rhs) {
+  ExplicitSchurComplementSolver* s = ExplicitSolver(h);
+  s->Eliminate(values, b, D);
+  const BlockRandomAccessSparseMatrix* m = s->lhs();
+  if (num_blocks) *num_blocks = (int)m->blocks().size();
+  if (num_cells) *num_cells = (int)m->cols().size();
+  if (num_values) *num_values = (int)m->values().size();
+  if (row_ptr) std::memcpy(row_ptr, m->row_ptr().data(), sizeof(int) * m->row_ptr().size());
+  if (cols) std::memcpy(cols, m->cols().data(), sizeof(int) * m->cols().size());
+  if (positions) std::memcpy(positions, m->positions().data(), sizeof(int) * m->positions().size());
+  if (lhs_values) std::memcpy(lhs_values, m->values().data(), sizeof(double) * m->values().size());
+  if (rhs) std::memcpy(rhs, s->rhs().data(), sizeof(double) * s->rhs().size());
+}
+
+// y += S x on the matrix of the last oracle_explicit_eliminate / oracle_explicit_solve.
+void oracle_explicit_multiply(OracleHandle* h, const double* x, double* y) {
+  ExplicitSolver(h)->lhs()->SymmetricRightMultiplyAndAccumulate(x, y);
+}
+
+// SchurComplementSolver::SolveImpl with SolveReducedLinearSystemUsingConjugateGradients.
+void oracle_explicit_solve(OracleHandle* h, const double* values, const double* b,
+                           const double* D, double q_tolerance, double r_tolerance,
+                           double* x, OracleSummary* out, double* trace, int max_trace) {
+  std::function<void(int, const Vec&)> tr = nullptr;
+  if (trace != nullptr && max_trace > 0) {
+    tr = [trace, max_trace](int it, const Vec& s) {
+      if (it <= max_trace)
+        std::memcpy(trace + (size_t)(it - 1) * s.size(), s.data(), sizeof(double) * s.size());
+    };
+  }
+  Summary s = ExplicitSolver(h)->Solve(values, b, D, q_tolerance, r_tolerance, x, tr);
+  if (out) {
+    out->residual_norm = s.residual_norm;
+    out->num_iterations = s.num_iterations;
+    out->termination_type = s.termination_type;
+    std::snprintf(out->message, sizeof(out->message), "%s", s.message.c_str());
+  }
 }
 
 // ConjugateGradientsSolver on a dense row-major SPD matrix with the identity

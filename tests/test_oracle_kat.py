@@ -222,3 +222,74 @@ def test_llt_inverse_uses_upper_triangle_only():
         out = np.zeros((n, n))
         ob.lib().oracle_inverse_small(ob._dp(np.ascontiguousarray(A)), n, ob._dp(out))
         np.testing.assert_allclose(out, np.linalg.inv(A), rtol=1e-11, atol=1e-13)
+
+
+# ---- use_explicit_schur_complement = true (oracle/explicit_schur.h) ----------
+def _dense_from_upper(row_ptr, cols, pos, vals, sizes):
+    """Dense symmetric matrix of a BlockRandomAccessSparseMatrix (upper block triangle)."""
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    S = np.zeros((off[-1], off[-1]))
+    for i in range(len(sizes)):
+        for k in range(row_ptr[i], row_ptr[i + 1]):
+            j = cols[k]
+            blk = vals[pos[k]:pos[k] + sizes[i] * sizes[j]].reshape(sizes[i], sizes[j])
+            S[off[i]:off[i + 1], off[j]:off[j + 1]] = blk
+            if i != j:
+                S[off[j]:off[j + 1], off[i]:off[i + 1]] = blk.T
+    return S
+
+
+# schur_eliminator_test.cc:127-226 (EliminateSolveAndCompare): lhs, rhs and the back
+# substituted solution against the dense Schur complement, with and without D.
+@pytest.mark.parametrize("pid", [2, 4, 5, 6])
+@pytest.mark.parametrize("use_D", [False, True])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_explicit_schur_eliminate_vs_dense(pid, use_D, threads):
+    if pid in (4, 6) and not use_D:
+        pytest.skip("rank deficient without regularisation")
+    st, values, b, D, _, o = make(pid, num_threads=threads)
+    Dv = D if use_D else None
+    A = st.dense(values)
+    ne = st.num_cols_e
+    S = dense_schur(A, Dv, ne)
+    H = A.T @ A + (np.diag(D * D) if use_D else 0)
+    g = A.T @ b
+    rhs_ref = g[ne:] - H[:ne, ne:].T @ np.linalg.solve(H[:ne, :ne], g[:ne])
+    row_ptr, cols, pos, vals, rhs = o.explicit_eliminate(values, b, Dv)
+    sizes = st.col_size[st.num_eliminate_blocks:]
+    got = _dense_from_upper(row_ptr, cols, pos, vals, sizes)
+    # only structurally non-zero pairs are stored; the dense S is zero elsewhere
+    np.testing.assert_allclose(got, S, atol=1e-12 * max(1.0, np.abs(S).max()))
+    np.testing.assert_allclose(rhs, rhs_ref, atol=1e-12 * max(1.0, np.abs(rhs_ref).max()))
+    # block_random_access_sparse_matrix_test.cc:126-141: symmetric multiply == dense
+    x = np.random.default_rng(pid).standard_normal(st.num_cols_f)
+    np.testing.assert_allclose(o.explicit_multiply(x), S @ x, atol=1e-12 * max(1.0, np.abs(S).max()))
+    assert all(cols[k] >= i for i in range(len(sizes)) for k in range(row_ptr[i], row_ptr[i + 1]))
+
+
+# solver_test.cc:1107-1140 allows ITERATIVE_SCHUR + use_explicit_schur_complement only with
+# SCHUR_JACOBI; the solve must agree with the dense normal equations like the implicit one.
+@pytest.mark.parametrize("pid", [2, 3, 4, 5, 6])
+@pytest.mark.parametrize("use_D", [False, True])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_explicit_schur_solver_vs_dense_and_implicit(pid, use_D, threads):
+    if pid in (4, 6) and not use_D:
+        pytest.skip("rank deficient without regularisation")
+    st, values, b, D, _, o = make(pid, num_threads=threads, preconditioner_type=ob.SCHUR_JACOBI,
+                                  max_num_iterations=st_cols(pid))
+    Dv = D if use_D else None
+    x, s = o.explicit_solve(values, b, Dv, q_tolerance=0.0, r_tolerance=1e-12)
+    ref = dense_solution(st.dense(values), b, Dv)
+    assert ob.TERMINATION[s["termination_type"]] == "SUCCESS", s
+    assert np.linalg.norm(x - ref) < 1e-12 * max(1.0, np.linalg.norm(ref)), s
+    xi, si = o.solve(values, b, Dv, q_tolerance=0.0, r_tolerance=1e-12)
+    assert si["num_iterations"] == s["num_iterations"]
+    np.testing.assert_allclose(x, xi, atol=1e-12 * max(1.0, np.abs(ref).max()))
+
+
+def test_explicit_schur_no_back_substitution_without_success():
+    """schur_complement_solver.cc:155-160: x keeps its zero point part unless CG succeeded."""
+    st, values, b, D, _, o = make(2, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=1)
+    x, s = o.explicit_solve(values, b, D, q_tolerance=0.0, r_tolerance=1e-30)
+    assert ob.TERMINATION[s["termination_type"]] == "NO_CONVERGENCE"
+    assert np.all(x[:st.num_cols_e] == 0.0) and np.any(x[st.num_cols_e:] != 0.0)
