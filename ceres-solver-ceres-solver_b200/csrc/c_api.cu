@@ -17,6 +17,7 @@
 #include "camera_kernels.cuh"
 #include "cg_kernels.cuh"
 #include "cg_step.cuh"
+#include "explicit_kernels.cuh"
 #include "kernels.cuh"
 #include "lm_kernels.cuh"
 #include "solver_state.h"
@@ -198,6 +199,14 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     return Fail(CB200_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
   if (o.residual_reset_period <= 0 || o.max_num_iterations < 0 || o.min_num_iterations < 0)
     return Fail(CB200_ERR_INVALID_ARGUMENT, "bad iteration options");
+  if (o.use_explicit_schur_complement) {  // solver.cc:277-290
+    if (o.preconditioner_type != CB200_SCHUR_JACOBI)
+      return Fail(CB200_ERR_INVALID_ARGUMENT,
+                  "use_explicit_schur_complement only supports SCHUR_JACOBI as the preconditioner.");
+    if (o.use_spse_initialization)
+      return Fail(CB200_ERR_INVALID_ARGUMENT,
+                  "use_explicit_schur_complement does not support use_spse_initialization.");
+  }
 
   FlatStructure flat;
   std::string err;
@@ -397,6 +406,27 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     TRY_CUDA(cudaMemcpy(&ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost));
     s->peer_allreduce = (ok == (double)o.world_size);
   }
+  if (o.use_explicit_schur_complement) {
+    // block structure of S from the GLOBAL problem (identical on every rank), destinations of
+    // this shard's outer products
+    const ExplicitStructure es = PlanExplicitStructure(flat);
+    const ExplicitFormPlan fp = PlanExplicitForm(es, row_start.data(), cam.data(), s->P_loc);
+    s->ex_cells = (int)es.col.size();
+    s->ex_items = (int)fp.items.size();
+    s->ex_row_ptr = es.row_ptr;
+    s->ex_col = es.col;
+    TRY(DeviceUpload(s, &s->d_ex_row_ptr, es.row_ptr));
+    TRY(DeviceUpload(s, &s->d_ex_col, es.col));
+    TRY(DeviceUpload(s, &s->d_ex_t_ptr, es.t_ptr));
+    TRY(DeviceUpload(s, &s->d_ex_t_cell, es.t_cell));
+    TRY(DeviceUpload(s, &s->d_ex_t_row, es.t_row));
+    TRY(DeviceUpload(s, &s->d_ex_srow, fp.srow));
+    TRY(DeviceUpload(s, &s->d_ex_pair_start, fp.pair_start));
+    TRY(DeviceUpload(s, &s->d_ex_pair_cell, fp.pair_cell));
+    TRY(DeviceUpload(s, &s->d_ex_items, fp.items));
+    TRY(DeviceAlloc(s, &s->d_ex_counter, 1));
+    TRY(DeviceAlloc(s, &s->d_S, (size_t)s->ex_cells * 81));
+  }
   s->global_dup_pairs = s->num_dup_pairs;
   if (o.world_size > 1) {
     // does any rank hold duplicate (point, camera) pairs? (decides whether the cross-term blocks are summed)
@@ -431,6 +461,20 @@ int cb200_shard_plan(const cb200_structure* structure, int num_eliminate_blocks,
   return CB200_OK;
 }
 
+int cb200_explicit_plan(const cb200_structure* structure, int num_eliminate_blocks, int* num_cells,
+                        int* row_ptr, int* cols) {
+  if (!structure) return Fail(CB200_ERR_INVALID_ARGUMENT, "null structure");
+  FlatStructure flat;
+  std::string err;
+  const int rc = Flatten(*structure, num_eliminate_blocks, &flat, &err);
+  if (rc != CB200_OK) return Fail(rc, err);
+  const ExplicitStructure es = PlanExplicitStructure(flat);
+  if (num_cells) *num_cells = (int)es.col.size();
+  if (row_ptr) std::copy(es.row_ptr.begin(), es.row_ptr.end(), row_ptr);
+  if (cols) std::copy(es.col.begin(), es.col.end(), cols);
+  return CB200_OK;
+}
+
 int cb200_num_rows(const cb200_solver* s) { return s ? 2 * s->N : 0; }
 int cb200_num_cols(const cb200_solver* s) { return s ? 3 * s->P + 9 * s->C : 0; }
 int cb200_num_cols_e(const cb200_solver* s) { return s ? 3 * s->P : 0; }
@@ -447,5 +491,6 @@ int cb200_shard(const cb200_solver* s, int* pb, int* pe, int* rb, int* re) {
 }  // extern "C"
 
 #include "c_api_solve.inc"
+#include "c_api_explicit.inc"
 #include "c_api_entry.inc"
 #include "c_api_lm.inc"

@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "cg_kernels.cuh"
+#include "explicit_plan.h"
 #include "flatten.h"
 
 namespace cb200 {
@@ -88,6 +89,17 @@ struct cb200_solver {
   double *d_lm_scalars = nullptr;  // cost, model, |x|^2, |delta|^2, gradient max, gradient norm^2
   double *h_lm_scalars = nullptr;  // pinned
   int eval_blocks = 0;
+
+  // explicit reduced camera matrix (use_explicit_schur_complement; explicit_kernels.cuh)
+  int ex_cells = 0, ex_items = 0;
+  int *d_ex_row_ptr = nullptr, *d_ex_col = nullptr, *d_ex_t_ptr = nullptr, *d_ex_t_cell = nullptr,
+      *d_ex_t_row = nullptr, *d_ex_srow = nullptr, *d_ex_counter = nullptr;
+  long long* d_ex_pair_start = nullptr;
+  unsigned int* d_ex_pair_cell = nullptr;
+  cb200::FormItem* d_ex_items = nullptr;
+  double* d_S = nullptr;  // ex_cells x 81
+  std::vector<int> ex_row_ptr, ex_col;  // host copy of the block structure (cb200_explicit_structure)
+  bool ex_ready = false;                // d_S holds the matrix of the resident values / D
 
   cb200::Nccl nccl;
   // fused all-reduce of the PCG step over NVLink peer memory (cg_step.cuh); null = NCCL path

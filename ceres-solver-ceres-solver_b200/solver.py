@@ -33,7 +33,7 @@ class COptions(ctypes.Structure):
                 ("max_num_spse_iterations", ctypes.c_int), ("spse_tolerance", ctypes.c_double),
                 ("device_id", ctypes.c_int), ("rank", ctypes.c_int), ("world_size", ctypes.c_int),
                 ("nccl_unique_id", ctypes.c_char_p), ("y_replicas", ctypes.c_int),
-                ("status_check_period", ctypes.c_int)]
+                ("status_check_period", ctypes.c_int), ("use_explicit_schur_complement", ctypes.c_int)]
 
 
 class CSummary(ctypes.Structure):
@@ -92,6 +92,10 @@ SYMBOLS = {
     "cb200_num_cols_f": (ctypes.c_int, [_H]),
     "cb200_shard": (ctypes.c_int, [_H, _ip, _ip, _ip, _ip]),
     "cb200_shard_plan": (ctypes.c_int, [ctypes.POINTER(CStructure), ctypes.c_int, ctypes.c_int, _ip, _ip]),
+    "cb200_explicit_plan": (ctypes.c_int, [ctypes.POINTER(CStructure), ctypes.c_int, _ip, _ip, _ip]),
+    "cb200_explicit_num_cells": (ctypes.c_int, [_H]),
+    "cb200_explicit_eliminate": (ctypes.c_int, [_H, _dp, _dp]),
+    "cb200_explicit_multiply": (ctypes.c_int, [_H, _dp, _dp]),
     "cb200_solve": (ctypes.c_int, [_H, _dp, _dp, _dp, ctypes.c_double, ctypes.c_double, _dp,
                                    ctypes.POINTER(CSummary)]),
     "cb200_upload": (ctypes.c_int, [_H, _dp, _dp, _dp]),
@@ -245,14 +249,15 @@ class IterativeSchurComplementSolver:
     def __init__(self, structure, preconditioner_type=SCHUR_JACOBI, min_num_iterations=0,
                  max_num_iterations=500, residual_reset_period=10, use_spse_initialization=False,
                  max_num_spse_iterations=5, spse_tolerance=0.1, device_id=0, rank=0, world_size=1,
-                 nccl_unique_id=None, y_replicas=0, status_check_period=0):
+                 nccl_unique_id=None, y_replicas=0, status_check_period=0,
+                 use_explicit_schur_complement=False):
         self.L = lib()
         self.structure = structure
         cs = structure.c_struct()
         opt = COptions(structure.num_eliminate_blocks, preconditioner_type, min_num_iterations,
                        max_num_iterations, residual_reset_period, int(use_spse_initialization),
                        max_num_spse_iterations, spse_tolerance, device_id, rank, world_size,
-                       nccl_unique_id, y_replicas, status_check_period)
+                       nccl_unique_id, y_replicas, status_check_period, int(use_explicit_schur_complement))
         h = _H()
         _check(self.L.cb200_create(ctypes.byref(cs), ctypes.byref(opt), ctypes.byref(h)))
         self.h = h
@@ -326,6 +331,20 @@ class IterativeSchurComplementSolver:
     def set_trace(self, max_trace):
         self._trace = np.zeros((max_trace, self.num_cols_f)) if max_trace else None
         _check(self.L.cb200_set_trace(self.h, _d(self._trace), max_trace))
+
+    # --- use_explicit_schur_complement seams -----------------------------------------------
+    def explicit_eliminate(self):
+        """(lhs cell values [num_cells x 81], reduced rhs) of SchurEliminator::Eliminate on the
+        resident values / b / D; the cell structure is explicit_plan(structure)."""
+        n = self.L.cb200_explicit_num_cells(self.h)
+        vals, rhs = np.zeros((n, 81)), np.zeros(self.num_cols_f)
+        _check(self.L.cb200_explicit_eliminate(self.h, _d(vals), _d(rhs)))
+        return vals, rhs
+
+    def explicit_multiply(self, x):
+        y = np.zeros(self.num_cols_f)
+        _check(self.L.cb200_explicit_multiply(self.h, _d(np.ascontiguousarray(x, dtype=np.float64)), _d(y)))
+        return y
 
     # --- finer-grained seams ---------------------------------------------------------------
     def pmv(self, op, x, y):
@@ -434,6 +453,19 @@ def shard_plan(structure, world_size):
     cs = structure.c_struct()
     _check(lib().cb200_shard_plan(ctypes.byref(cs), structure.num_eliminate_blocks, world_size, _i(pb), _i(rb)))
     return pb, rb
+
+
+def explicit_plan(structure):
+    """(row_ptr, cols): block CRS of the upper triangle of the explicit Schur complement
+    (SparseSchurComplementSolver::InitStorage), host only."""
+    cs = structure.c_struct()
+    n = ctypes.c_int()
+    _check(lib().cb200_explicit_plan(ctypes.byref(cs), structure.num_eliminate_blocks, ctypes.byref(n), None, None))
+    C = len(structure.col_size) - structure.num_eliminate_blocks
+    row_ptr = np.zeros(C + 1, dtype=np.int32)
+    cols = np.zeros(n.value, dtype=np.int32)
+    _check(lib().cb200_explicit_plan(ctypes.byref(cs), structure.num_eliminate_blocks, None, _i(row_ptr), _i(cols)))
+    return row_ptr, cols
 
 
 def nccl_unique_id():

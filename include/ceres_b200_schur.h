@@ -88,6 +88,13 @@ typedef struct cb200_options {
                                  accumulator that spread FP64 atomics           */
   int status_check_period;    /* 0 = default; PCG iterations launched between
                                  two reads of the device convergence flag       */
+  int use_explicit_schur_complement; /* linear_solver.h:161, linear_solver.cc:111-116:
+                                 form the reduced camera matrix S as a block-sparse
+                                 matrix once per solve and run PCG on it
+                                 (SparseSchurComplementSolver::
+                                 SolveReducedLinearSystemUsingConjugateGradients,
+                                 schur_complement_solver.cc:337-408). SCHUR_JACOBI only,
+                                 no SPSE initialisation (solver.cc:277-290).          */
 } cb200_options;
 
 /* LinearSolver::Summary (linear_solver.h:320-326) + per-phase device timings. */
@@ -126,6 +133,15 @@ void cb200_destroy(cb200_solver* s);
  * block_sparse_matrix.cc:58-67). Both outputs have world_size + 1 entries. */
 int cb200_shard_plan(const cb200_structure* structure, int num_eliminate_blocks, int world_size,
                      int* point_bounds, int* row_bounds);
+
+/* The block structure cb200_create gives the explicit Schur complement, without a
+ * device (host only): SparseSchurComplementSolver::InitStorage
+ * (schur_complement_solver.cc:224-290) + the BlockRandomAccessSparseMatrix layout
+ * (block_random_access_sparse_matrix.cc:47-103). Upper block triangle in block CRS,
+ * columns ascending, cell k holds 81 row-major doubles at 81 k. row_ptr (C + 1) and
+ * cols (*num_cells) may be NULL to query the size. */
+int cb200_explicit_plan(const cb200_structure* structure, int num_eliminate_blocks,
+                        int* num_cells, int* row_ptr, int* cols);
 
 /* Page-lock a caller-owned host buffer (cudaHostRegister) so that cb200_solve /
  * cb200_upload copy from it at full PCIe rate instead of through the driver's
@@ -223,6 +239,18 @@ int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
  * 9 / 10 Right / Left F, 11 UpdateBlockDiagonalFtF, 12 PSE preconditioner apply. */
 int cb200_time_op(cb200_solver* s, int op, int warmup, int iters, float* ms_out,
                   int* launches_out);
+
+/* ---- use_explicit_schur_complement seams (solvers created with the option) ----
+ * cb200_explicit_eliminate: SchurEliminator::Eliminate on the resident values / b / D
+ * (schur_eliminator_impl.h:176-304): lhs_values (num_cells x 81, the structure of
+ * cb200_explicit_plan; NULL to skip) and the reduced rhs (9C; NULL to skip).
+ * cb200_explicit_multiply: y = S x,
+ * BlockRandomAccessSparseMatrix::SymmetricRightMultiplyAndAccumulate
+ * (block_random_access_sparse_matrix.cc:128-170) on the matrix of the last
+ * eliminate / solve. */
+int cb200_explicit_num_cells(const cb200_solver* s);
+int cb200_explicit_eliminate(cb200_solver* s, double* lhs_values, double* rhs);
+int cb200_explicit_multiply(cb200_solver* s, const double* x, double* y);
 
 /* ---- widened boundary: the Snavely bundle-adjustment
  * evaluator and the trust-region loop run on the device-resident problem, so the

@@ -105,3 +105,32 @@ def test_adapter_header_flattens_a_ceres_block_structure(tmp_path):
     sh = [int(t) for t in kv["shard"].split(",")]
     assert sh[0] == 0 and sh[3] == 40 and sh[0] <= sh[1] <= sh[2] <= sh[3], out
     assert kv["create"] == ("0" if util.has_gpu() else "-3"), out
+
+
+@pytest.mark.parametrize("shape", [(6, 40, 150, 0), (31, 800, 3500, 4), (3, 50, 120, 2)])
+def test_explicit_schur_block_structure_matches_init_storage(shape):
+    """cb200_explicit_plan (host only) == SparseSchurComplementSolver::InitStorage +
+    BlockRandomAccessSparseMatrix layout as restated by the oracle."""
+    from oracle import binding as ob
+    m = util.pkg()
+    C, P, N, dup = shape
+    p = m.SyntheticBAL(C, P, N, seed=3, dup_pairs=dup)
+    cost, residuals, values = p.evaluate()
+    row_ptr, cols = m.explicit_plan(p.structure)
+    o = ob.Oracle(util.oracle_structure(p.structure))
+    o_row_ptr, o_cols, o_pos, _, _ = o.explicit_eliminate(values, residuals, None)
+    assert np.array_equal(row_ptr, o_row_ptr) and np.array_equal(cols, o_cols)
+    assert np.array_equal(o_pos, 81 * np.arange(len(cols)))  # cell k lives at 81 k
+    assert all(cols[row_ptr[i]] == i for i in range(C))  # diagonal cell first in every row
+
+
+def test_explicit_schur_option_validation():
+    """solver.cc:277-290: SCHUR_JACOBI only, no SPSE initialisation (checked before any device work)."""
+    m = util.pkg()
+    p = m.SyntheticBAL(5, 20, 60, geometry=False)
+    with pytest.raises(m.B200Error, match="only supports SCHUR_JACOBI"):
+        m.IterativeSchurComplementSolver(p.structure, preconditioner_type=m.JACOBI,
+                                         use_explicit_schur_complement=True)
+    with pytest.raises(m.B200Error, match="does not support use_spse_initialization"):
+        m.IterativeSchurComplementSolver(p.structure, use_spse_initialization=True,
+                                         use_explicit_schur_complement=True)
