@@ -112,3 +112,57 @@ def test_two_gpu_lm_loop_matches_reference_loop():
         assert util.rel_err(cam, want["cameras"]) < 1e-7
         pts_all[3 * pb:3 * pe] = pts[3 * pb:3 * pe]
     assert util.rel_err(pts_all, want["points"]) < 1e-7
+
+
+def _explicit_worker(rank, world, uid, out):
+    m = util.pkg()
+    p = m.SyntheticBAL.named("ladybug", scale=0.05)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    g = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=300,
+                                         device_id=rank, rank=rank, world_size=world, nccl_unique_id=uid,
+                                         use_explicit_schur_complement=True)
+    x = np.full(p.structure.num_cols, np.nan)
+    x, s = g.solve(values, residuals, D, 1e-3, -1.0, x=x)
+    cells, rhs = g.explicit_eliminate()
+    sx = g.explicit_multiply(np.arange(9 * p.C, dtype=np.float64) / (9 * p.C))
+    out[rank] = (x, s["num_iterations"], s["termination_type"], g.point_begin, g.point_end, cells, rhs, sx)
+    g.close()
+
+
+def test_two_gpu_explicit_schur_matches_oracle():
+    """use_explicit_schur_complement with the points sharded over two GPUs: every rank forms the outer
+    products of its own points, the cells are summed over the ranks (NCCL), PCG on the explicit matrix
+    runs replicated and bit-identical on both."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from oracle import binding as ob
+    m = util.pkg()
+    world = 2
+    uid = m.nccl_unique_id()
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    procs = [ctx.Process(target=_explicit_worker, args=(r, world, uid, out)) for r in range(world)]
+    for pr in procs:
+        pr.start()
+    for pr in procs:
+        pr.join(300)
+        assert pr.exitcode == 0
+    p = m.SyntheticBAL.named("ladybug", scale=0.05)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    o = ob.Oracle(util.oracle_structure(p.structure), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI,
+                  max_num_iterations=300)
+    xo, so = o.explicit_solve(values, residuals, D, 1e-3, -1.0)
+    _, _, _, want_cells, want_rhs = o.explicit_eliminate(values, residuals, D)
+    sxo = o.explicit_multiply(np.arange(9 * p.C, dtype=np.float64) / (9 * p.C))
+    ne = 3 * p.P
+    for r in range(world):
+        x, its, term, pb, pe, cells, rhs, sx = out[r]
+        assert its == so["num_iterations"] and term == so["termination_type"]
+        assert util.rel_err(cells.reshape(-1), want_cells) < 1e-12
+        assert util.rel_err(rhs, want_rhs) < 1e-12
+        assert util.rel_err(sx, sxo) < 1e-12
+        assert util.rel_err(x[ne:], xo[ne:]) < 1e-9
+        assert util.rel_err(x[3 * pb:3 * pe], xo[3 * pb:3 * pe]) < 1e-9
+    # replicated PCG: both ranks hold the same camera solution bit for bit
+    assert np.array_equal(out[0][0][ne:], out[1][0][ne:])
+    assert np.array_equal(out[0][5], out[1][5])

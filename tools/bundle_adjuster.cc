@@ -108,7 +108,7 @@ int main(int argc, char** argv) {
     return Die("only --linear_solver=iterative_schur runs on this path (got " + flags.Str("linear_solver") + ")");
   if (flags.Str("trust_region_strategy") != "levenberg_marquardt")
     return Die("only --trust_region_strategy=levenberg_marquardt is implemented");
-  for (const char* k : {"explicit_schur_complement", "inner_iterations", "use_quaternions", "use_manifolds", "robustify",
+  for (const char* k : {"inner_iterations", "use_quaternions", "use_manifolds", "robustify",
                         "line_search", "nonmonotonic_steps", "mixed_precision_solves"})
     if (flags.Bool(k)) return Die(std::string("--") + k + " is not implemented on this path");
   const int precond = PreconditionerCode(flags.Str("preconditioner"));
@@ -172,6 +172,7 @@ int main(int argc, char** argv) {
   o.use_spse_initialization = flags.Bool("use_spse_initialization");
   o.max_num_spse_iterations = flags.Int("max_num_spse_iterations");
   o.spse_tolerance = flags.Double("spse_tolerance");
+  o.use_explicit_schur_complement = flags.Bool("explicit_schur_complement");  // bundle_adjuster.cc:91,168
   o.device_id = flags.Int("device");
   o.rank = 0;
   o.world_size = 1;
