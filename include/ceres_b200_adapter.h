@@ -112,6 +112,9 @@ class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver 
       o.use_spse_initialization = options_.use_spse_initialization;
       o.max_num_spse_iterations = options_.max_num_spse_iterations;
       o.spse_tolerance = options_.spse_tolerance;
+      // linear_solver.cc:111-113: the same adapter serves ITERATIVE_SCHUR with and without the
+      // explicit reduced camera matrix (SparseSchurComplementSolver's CG branch)
+      o.use_explicit_schur_complement = options_.use_explicit_schur_complement;
       o.device_id = 0;
       o.rank = 0;
       o.world_size = 1;
