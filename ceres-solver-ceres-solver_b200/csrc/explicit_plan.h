@@ -127,6 +127,43 @@ inline ExplicitFormPlan PlanExplicitForm(const ExplicitStructure& es, const int*
     }
     for (int u0 = 0; u0 < k; u0 += kFormRows) plan.items.push_back(FormItem{p, u0});
   }
+  // Order of execution. The cells a point touches lie in the block rows of its cameras, and S is 2-3x
+  // the L2 at Ladybug / Venice shape: in point order (random home cameras) every reduction into it
+  // missed (11 GB of DRAM traffic for 1.3 GB of data at Venice). So items are grouped by their point's
+  // smallest camera into camera ranges whose rows of S fit a quarter of the L2, and inside a group
+  // they are dealt round-robin over the group's cameras: warps that run at the same time hit the
+  // same resident rows, but not the same cells (same-address reductions serialise).
+  {
+    const int C = es.num_cameras;
+    auto key = [&](const FormItem& it) { return cam[plan.srow[row_start[it.point]]]; };
+    std::vector<int> bucket_start(C + 1, 0);
+    for (const FormItem& it : plan.items) ++bucket_start[key(it) + 1];
+    for (int c = 0; c < C; ++c) bucket_start[c + 1] += bucket_start[c];
+    std::vector<FormItem> by_camera(plan.items.size());
+    {
+      std::vector<int> cursor(bucket_start.begin(), bucket_start.end() - 1);
+      for (const FormItem& it : plan.items) by_camera[cursor[key(it)]++] = it;
+    }
+    constexpr long long kGroupBytes = 32LL << 20;
+    size_t out = 0;
+    for (int c0 = 0; c0 < C;) {
+      int c1 = c0;
+      long long bytes = 0;
+      while (c1 < C && (c1 == c0 || bytes < kGroupBytes)) {
+        bytes += 648LL * (es.row_ptr[c1 + 1] - es.row_ptr[c1]);
+        ++c1;
+      }
+      bool any = true;
+      for (int round = 0; any; ++round) {
+        any = false;
+        for (int c = c0; c < c1; ++c) {
+          const int idx = bucket_start[c] + round;
+          if (idx < bucket_start[c + 1]) { plan.items[out++] = by_camera[idx]; any = true; }
+        }
+      }
+      c0 = c1;
+    }
+  }
   return plan;
 }
 
