@@ -158,3 +158,30 @@ def test_explicit_and_implicit_solves_agree_at_lm_shape():
     xi, si = gi.solve(values, residuals, D, 1e-3, -1.0)
     assert si["num_iterations"] == se["num_iterations"]
     assert util.rel_err(xe, xi) < ITERATE_TOL
+
+
+def test_lm_loop_with_explicit_schur_matches_reference_loop():
+    """The device trust-region loop (cb200_lm_minimize) on a handle created with
+    use_explicit_schur_complement, against the CPU restatement of the loop driving the oracle's explicit
+    solver: same accepted steps, same PCG iteration counts, costs within 1e-8 relative."""
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    p = m.SyntheticBAL(31, 3000, 14000, seed=7, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    st = p.structure
+    o = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=500)
+    want = lmr.minimize(p, p.cameras, p.points, lambda v, r, D, e: o.explicit_solve(v, r, D, e, -1.0), eta=1e-2,
+                        max_num_iterations=8)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=500,
+                                         use_explicit_schur_complement=True)
+    g.bal_attach(p.observations)
+    g.bal_set_parameters(p.cameras, p.points)
+    got = g.lm_minimize(eta=1e-2, max_num_iterations=8)
+    assert got["termination_type"] == want["termination_type"]
+    assert len(got["iterations"]) == len(want["iterations"])
+    for a, b in zip(got["iterations"], want["iterations"]):
+        assert a["iteration"] == b["iteration"]
+        assert bool(a["step_is_successful"]) == bool(b["step_is_successful"])
+        assert a["linear_solver_iterations"] == b["linear_solver_iterations"], (a, b)
+        assert abs(a["cost"] - b["cost"]) <= 1e-8 * b["cost"], (a, b)
+    assert abs(got["final_cost"] - want["final_cost"]) <= 1e-8 * want["final_cost"]
+    assert want["final_cost"] < 0.2 * want["initial_cost"]
