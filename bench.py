@@ -150,6 +150,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-lm", action="store_true", help="skip the device-resident LM loop measurement")
     ap.add_argument("--no-cusparse", action="store_true", help="skip the cuSPARSE CSR comparison of S*x")
+    ap.add_argument("--no-explicit", action="store_true",
+                    help="skip the use_explicit_schur_complement comparison (SURVEY 8(f) row 3)")
     ap.add_argument("--lm-iterations", type=int, default=10)
     ap.add_argument("--precond", default="schur_jacobi", choices=["schur_jacobi", "spse", "jacobi", "identity"])
     args = ap.parse_args()
@@ -292,6 +294,37 @@ def main():
               "note": "cb200_lm_minimize: device Snavely evaluator + ITERATIVE_SCHUR solve + step evaluation per "
                       "iteration; timed from host parameter buffers to host parameter buffers"}
 
+    # ---- the same solve with use_explicit_schur_complement (explicit block-sparse S) ----
+    explicit = None
+    if world == 1 and not args.no_explicit and args.precond == "schur_jacobi":
+        try:
+            g.upload_ptr(hv.data_ptr(), hb.data_ptr(), hD.data_ptr())
+            si = g.solve_resident(ETA, -1.0)
+            xi = g.download_solution()
+            ge = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=PRECOND[args.precond],
+                                                    max_num_iterations=MAX_PCG, device_id=local_rank,
+                                                    use_explicit_schur_complement=True)
+            ge.upload_ptr(hv.data_ptr(), hb.data_ptr(), hD.data_ptr())
+            ge.solve_resident(ETA, -1.0)
+            ms = 0.0
+            for _ in range(5):
+                se = ge.solve_resident(ETA, -1.0)
+                ms += (se["setup_ms"] + se["pcg_ms"] + se["back_substitute_ms"]) / 5
+            xe = ge.download_solution()
+            form_ms, _ = ge.time_op(13, warmup=1, iters=5)
+            spmv_ms, _ = ge.time_op(15, warmup=2, iters=20)
+            cells = len(pkg.explicit_plan(p.structure)[1])
+            explicit = {"ms_per_step": ms, "steps_per_sec": 1e3 / ms, "pcg_iterations": se["num_iterations"],
+                        "implicit_pcg_iterations": si["num_iterations"], "eliminate_ms": form_ms,
+                        "explicit_sx_ms": spmv_ms, "implicit_sx_ms": sx_ms, "upper_cells": cells,
+                        "S_bytes": 648 * cells, "rel_diff_of_solutions": float(np.linalg.norm(xe - xi) / np.linalg.norm(xi)),
+                        "note": "same handle type created with use_explicit_schur_complement: SchurEliminator::Eliminate "
+                                "into a block-sparse S + PCG on it; slower than the implicit operator at this shape "
+                                "(DESIGN.md 7.2), reported for completeness"}
+            ge.close()
+        except Exception as e:  # a comparison, never a reason to lose the bench line
+            explicit = {"unavailable": repr(e)[:200]}
+
     if rank == 0:
         line = {"metric": "lm_linear_solves_per_sec", "value": args.steps / (dev_ms * 1e-3), "unit": "LM iters/s",
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps,
@@ -303,7 +336,8 @@ def main():
                 "e2e": {"value": args.steps / (e2e_ms * 1e-3), "unit": "LM iters/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps,
                         "wall_ms_per_step": e2e_wall_ms / args.steps, "h2d_ms": s2["h2d_ms"], "d2h_ms": s2["d2h_ms"]},
-                "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "lm_loop": lm}
+                "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "lm_loop": lm,
+                "explicit_schur": explicit}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(p, values, residuals, D, PRECOND[args.precond])
         print(json.dumps(line), flush=True)
