@@ -41,6 +41,30 @@ def algorithmic_bytes_sx(N, P, C):
     return 192 * N + 4 * N + 4 * P + 72 * P + 2 * 72 * C
 
 
+def bind_to_gpu_numa_node(device):
+    """Multi-rank runs: keep this process (and therefore the pages of the pinned host buffers it allocates
+    next) on the CPUs NVML reports as local to its GPU. Ranks started by torchrun float over both sockets;
+    a pinned buffer on the far socket makes every H2D copy cross the inter-socket link, and the timed value
+    is the max over ranks. Returns the CPU list, or None when NVML / the affinity call is unavailable."""
+    if os.environ.get("CB200_NO_NUMA_BIND"):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cpus = [c for c in cpus if c in allowed]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return cpus
+    except Exception:
+        pass
+    return None
+
+
 class ClockSampler:
     """SM clock and throttle reasons sampled (NVML, every 10 ms, own thread) DURING the timed region."""
 
@@ -163,6 +187,7 @@ def main():
         return
     args.warmup = max(args.warmup, 3)
 
+    numa_cpus = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
@@ -335,6 +360,7 @@ def main():
                 "termination": s["message"],
                 "e2e": {"value": args.steps / (e2e_ms * 1e-3), "unit": "LM iters/s", "h2d_bytes_per_step": h2d,
                         "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / args.steps,
+                        "host_cpus_bound_to_gpu_numa_node": len(numa_cpus) if numa_cpus else None,
                         "wall_ms_per_step": e2e_wall_ms / args.steps, "h2d_ms": s2["h2d_ms"], "d2h_ms": s2["d2h_ms"]},
                 "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "lm_loop": lm,
                 "explicit_schur": explicit}
