@@ -151,7 +151,7 @@ explicit_diag_kernel(double* __restrict__ S, const int* __restrict__ row_ptr, co
   for (int k = 0; k < 81; ++k) sj[(size_t)c * 81 + k] = m[k];
 }
 
-constexpr int kSpmvWarps = 4;
+constexpr int kSpmvWarps = 8;
 constexpr int kSpmvThreads = 32 * kSpmvWarps;
 
 // y = S x with the upper block triangle stored: CTA i gathers the cells (i, j >= i) of its row
@@ -173,22 +173,35 @@ explicit_spmv_kernel(const int* done, const double* __restrict__ S, const int* _
   const int u_begin = row_ptr[i], nU = row_ptr[i + 1] - u_begin;
   const int l_begin = t_ptr[i], nL = t_ptr[i + 1] - l_begin;
   double up = 0.0, lo0 = 0.0, lo1 = 0.0, lo2 = 0.0;
-  for (int w = warp; w < nU; w += kSpmvWarps) {
-    const int k = u_begin + w;
-    const int jc = col[k];
+  // two cells per step: both cells' six loads are in flight before the first multiply
+  for (int w = warp; w < nU; w += 2 * kSpmvWarps) {
+    const int k0 = u_begin + w;
+    const bool two = w + kSpmvWarps < nU;
+    const int k1 = two ? k0 + kSpmvWarps : k0;
+    const int j0 = col[k0], j1 = col[k1];
     if (active) {
-      const double* c = S + (size_t)k * 81 + a * 9 + 3 * g;
-      const double* xj = x + (size_t)jc * 9 + 3 * g;
-      up += c[0] * xj[0] + c[1] * xj[1] + c[2] * xj[2];
+      const double* c0 = S + (size_t)k0 * 81 + a * 9 + 3 * g;
+      const double* c1 = S + (size_t)k1 * 81 + a * 9 + 3 * g;
+      const double* x0 = x + (size_t)j0 * 9 + 3 * g;
+      const double* x1 = x + (size_t)j1 * 9 + 3 * g;
+      const double a0 = c0[0], a1 = c0[1], a2 = c0[2], b0 = c1[0], b1 = c1[1], b2 = c1[2];
+      const double p0 = x0[0], p1 = x0[1], p2 = x0[2], q0 = x1[0], q1 = x1[1], q2 = x1[2];
+      up += a0 * p0 + a1 * p1 + a2 * p2;
+      if (two) up += b0 * q0 + b1 * q1 + b2 * q2;
     }
   }
-  for (int w = warp; w < nL; w += kSpmvWarps) {
-    const int k = t_cell[l_begin + w];
-    const int rc = t_row[l_begin + w];
+  for (int w = warp; w < nL; w += 2 * kSpmvWarps) {
+    const bool two = w + kSpmvWarps < nL;
+    const int t0 = l_begin + w, t1 = two ? t0 + kSpmvWarps : t0;
+    const int k0 = t_cell[t0], k1 = t_cell[t1];
+    const int r0 = t_row[t0], r1 = t_row[t1];
     if (active) {
-      const double* c = S + (size_t)k * 81 + a * 9 + 3 * g;
-      const double xr = x[(size_t)rc * 9 + a];
-      lo0 += c[0] * xr; lo1 += c[1] * xr; lo2 += c[2] * xr;
+      const double* c0 = S + (size_t)k0 * 81 + a * 9 + 3 * g;
+      const double* c1 = S + (size_t)k1 * 81 + a * 9 + 3 * g;
+      const double a0 = c0[0], a1 = c0[1], a2 = c0[2], b0 = c1[0], b1 = c1[1], b2 = c1[2];
+      const double xr0 = x[(size_t)r0 * 9 + a], xr1 = two ? x[(size_t)r1 * 9 + a] : 0.0;
+      lo0 += a0 * xr0; lo1 += a1 * xr0; lo2 += a2 * xr0;
+      lo0 += b0 * xr1; lo1 += b1 * xr1; lo2 += b2 * xr1;
     }
   }
   if (active) {
