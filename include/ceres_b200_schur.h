@@ -236,7 +236,9 @@ int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
  * op: 0 S*x (isc multiply), 1 EtE inverse build, 2 rhs, 3 Schur-Jacobi build,
  * 4 back substitute, 6 the fused S*x kernel alone; the separate products that the
  * reference's evaluation_benchmark.cc times (:333-491): 7 / 8 Right / Left E,
- * 9 / 10 Right / Left F, 11 UpdateBlockDiagonalFtF, 12 PSE preconditioner apply. */
+ * 9 / 10 Right / Left F, 11 UpdateBlockDiagonalFtF, 12 PSE preconditioner apply;
+ * explicit-Schur solvers: 13 SchurEliminator::Eliminate (rhs pass + outer products +
+ * diagonal), 14 the outer-product kernel alone, 15 S*x on the explicit matrix. */
 int cb200_time_op(cb200_solver* s, int op, int warmup, int iters, float* ms_out,
                   int* launches_out);
 

@@ -185,3 +185,25 @@ def test_lm_loop_with_explicit_schur_matches_reference_loop():
         assert abs(a["cost"] - b["cost"]) <= 1e-8 * b["cost"], (a, b)
     assert abs(got["final_cost"] - want["final_cost"]) <= 1e-8 * want["final_cost"]
     assert want["final_cost"] < 0.2 * want["initial_cost"]
+
+
+def test_explicit_seams_report_call_order_errors():
+    """Programmer errors come back as negative status codes with a message, never as a crash
+    (SURVEY 8(b) "Errors")."""
+    m, st, values, b, D = problem()
+    gi = m.IterativeSchurComplementSolver(st)
+    gi.upload(values, b, D)
+    with pytest.raises(m.B200Error, match="error -5"):
+        gi.explicit_eliminate()          # not created with use_explicit_schur_complement
+    with pytest.raises(m.B200Error, match="error -5"):
+        gi.explicit_multiply(np.zeros(st.num_cols_f))
+    ge = m.IterativeSchurComplementSolver(st, use_explicit_schur_complement=True)
+    with pytest.raises(m.B200Error, match="error -5"):
+        ge.explicit_multiply(np.zeros(st.num_cols_f))   # nothing eliminated yet
+    with pytest.raises(m.B200Error, match="error -5"):
+        ge.explicit_eliminate()                          # nothing uploaded
+    ge.upload(values, b, D)
+    ge.explicit_eliminate()
+    ge.upload(values)                                    # new values invalidate the matrix
+    with pytest.raises(m.B200Error, match="error -5"):
+        ge.explicit_multiply(np.zeros(st.num_cols_f))

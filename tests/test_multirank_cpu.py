@@ -58,6 +58,17 @@ def _worker(rank, world, port, out):
         Df2 = D[3 * p.P:] ** 2
         parts = {"rhs": o.isc_rhs(), "sx": o.isc_multiply(x),
                  "sj": o.schur_jacobi(v, Ds_nocam, invert=False).reshape(-1)}
+        # use_explicit_schur_complement: every rank forms the cells of its own points in the GLOBAL block
+        # structure (cb200_explicit_plan, host only); the cells are summed over the ranks
+        grow, gcols = m.explicit_plan(p.structure)
+        lrow, lcols, lpos, lvals, lrhs = o.explicit_eliminate(v, bs, Ds_nocam)
+        cells = np.zeros((len(gcols), 81))
+        for i in range(p.C):
+            idx = grow[i] + np.searchsorted(gcols[grow[i]:grow[i + 1]], lcols[lrow[i]:lrow[i + 1]])
+            assert np.array_equal(gcols[idx], lcols[lrow[i]:lrow[i + 1]])  # a shard's pairs are a subset
+            cells[idx] = lvals.reshape(-1, 81)[lrow[i]:lrow[i + 1]]
+        parts["cells"] = cells.reshape(-1)
+        parts["rhs_explicit"] = lrhs
         for k in parts:
             t = torch.from_numpy(parts[k].copy())
             dist.all_reduce(t)
@@ -70,6 +81,10 @@ def _worker(rank, world, port, out):
         full.isc_init(values, D, b)
         want = {"rhs": full.isc_rhs(), "sx": full.isc_multiply(x),
                 "sj": full.schur_jacobi(values, D, invert=False).reshape(-1)}
+        _, _, _, fvals, frhs = full.explicit_eliminate(values, b, D)
+        gc = parts["cells"].reshape(-1, 9, 9)
+        gc[grow[:-1]] += np.stack([np.diag(d) for d in Df2.reshape(-1, 9)])  # D_f^2 once, after the sum
+        want["cells"], want["rhs_explicit"] = fvals, frhs
         errs = {k: util.rel_err(parts[k], want[k]) for k in want}
         errs["back"] = util.rel_err(back, full.isc_back_substitute(x)[3 * p0:3 * p1])
         errs["rows"] = float(abs((r1 - r0) - p.N / world) / p.N)
@@ -92,7 +107,7 @@ def test_point_sharded_sum_equals_unsharded_world2():
         assert pr.exitcode == 0
     for r in range(world):
         errs = out[r]
-        for k in ("rhs", "sx", "sj", "back"):
+        for k in ("rhs", "sx", "sj", "back", "cells", "rhs_explicit"):
             assert errs[k] < 1e-12, (r, k, errs)
         assert errs["rows"] < 0.02, errs  # balanced observation counts
 
