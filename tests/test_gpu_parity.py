@@ -415,8 +415,9 @@ def test_lm_final_cost_matches_reference_loop(eta):
     assert util.rel_err(cam, want["cameras"]) < 1e-7 and util.rel_err(pts, want["points"]) < 1e-7
 
 
-def test_bundle_adjuster_cli_matches_reference_loop(tmp_path):
-    """the bundle_adjuster CLI (BAL file -> Normalize -> Perturb -> LM with
+@pytest.mark.parametrize("explicit", [False, True])
+def test_bundle_adjuster_cli_matches_reference_loop(tmp_path, explicit):
+    """(explicit: --explicit_schur_complement, examples/bundle_adjuster.cc:91,168.) SURVEY 8(f) rank 4: the bundle_adjuster CLI (BAL file -> Normalize -> Perturb -> LM with
     ITERATIVE_SCHUR on the device) against the same flow on the CPU: oracle/bal_reference-checked
     file handling + the restated trust-region loop + the oracle linear solver."""
     import re
@@ -428,7 +429,8 @@ def test_bundle_adjuster_cli_matches_reference_loop(tmp_path):
     cli = m._build.build_cli()
     r = subprocess.run([cli, f"--input={tmp_path / 'in.txt'}", "--num_iterations=6", "--eta=1e-2",
                         "--preconditioner=schur_jacobi", f"--final_bal={tmp_path / 'out.txt'}",
-                        f"--final_ply={tmp_path / 'out.ply'}"], capture_output=True, text=True, timeout=300)
+                        f"--final_ply={tmp_path / 'out.ply'}"] + (["--explicit_schur_complement"] if explicit else []),
+                       capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr
     initial = float(re.search(r"Initial\s+(\S+)", r.stdout).group(1))
     final = float(re.search(r"Final\s+(\S+)", r.stdout).group(1))
@@ -440,7 +442,9 @@ def test_bundle_adjuster_cli_matches_reference_loop(tmp_path):
     q = f.problem()
     o = ob.Oracle(util.oracle_structure(q.structure), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI,
                   max_num_iterations=500)
-    want = lmr.minimize(q, q.cameras, q.points, lambda v, rr, D, e: o.solve(v, rr, D, e, -1.0), eta=1e-2,
+    solve = (lambda v, rr, D, e: o.explicit_solve(v, rr, D, e, -1.0)) if explicit else \
+            (lambda v, rr, D, e: o.solve(v, rr, D, e, -1.0))
+    want = lmr.minimize(q, q.cameras, q.points, solve, eta=1e-2,
                         max_num_iterations=6, function_tolerance=1e-16, gradient_tolerance=1e-16,
                         parameter_tolerance=1e-16)
     assert abs(initial - want["initial_cost"]) <= 2e-6 * want["initial_cost"]  # printed with 7 digits
