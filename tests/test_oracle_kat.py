@@ -293,3 +293,66 @@ def test_explicit_schur_no_back_substitution_without_success():
     x, s = o.explicit_solve(values, b, D, q_tolerance=0.0, r_tolerance=1e-30)
     assert ob.TERMINATION[s["termination_type"]] == "NO_CONVERGENCE"
     assert np.all(x[:st.num_cols_e] == 0.0) and np.any(x[st.num_cols_e:] != 0.0)
+
+
+def _random_schur_problem(seed, e_size, f_sizes, row_size, num_e=7, trailing_rows=3):
+    """A random block structure in the shape schur_eliminator_test.cc:228-330 builds by hand
+    (static or mixed block sizes, rows with one e cell and 1..3 f cells, and rows WITHOUT an e
+    cell at the bottom: NoEBlockRowsUpdate, schur_eliminator_impl.h:566-593)."""
+    rng = np.random.default_rng(seed)
+    nf = len(f_sizes)
+    col_size = [e_size] * num_e + list(f_sizes)
+    col_pos = np.concatenate([[0], np.cumsum(col_size)[:-1]])
+    row_sz, row_pos, cell_ptr, cid, cpos = [], [], [0], [], []
+    pos, rp = 0, 0
+    for e in range(num_e):
+        for _ in range(int(rng.integers(1, 5))):
+            rs = row_size if row_size > 0 else int(rng.integers(1, 4))
+            fs = sorted(rng.choice(nf, size=int(rng.integers(1, min(3, nf) + 1)), replace=False))
+            row_sz.append(rs); row_pos.append(rp); rp += rs
+            for b in [e] + [num_e + int(f) for f in fs]:
+                cid.append(b); cpos.append(pos); pos += rs * col_size[b]
+            cell_ptr.append(len(cid))
+    for _ in range(trailing_rows):
+        rs = row_size if row_size > 0 else int(rng.integers(1, 4))
+        fs = sorted(rng.choice(nf, size=int(rng.integers(1, min(3, nf) + 1)), replace=False))
+        row_sz.append(rs); row_pos.append(rp); rp += rs
+        for f in fs:
+            cid.append(num_e + int(f)); cpos.append(pos); pos += rs * col_size[num_e + int(f)]
+        cell_ptr.append(len(cid))
+    st = ob.Structure(row_sz, row_pos, cell_ptr, cid, cpos, col_size, col_pos, num_e)
+    values = rng.standard_normal(pos)
+    b = rng.standard_normal(rp)
+    D = np.abs(rng.standard_normal(int(sum(col_size)))) + 0.5
+    return st, values, b, D
+
+
+@pytest.mark.parametrize("shape", [
+    (3, [9] * 6, 2),            # the bundle-adjustment structure <2,3,9>
+    (3, [3, 4, 9, 2, 6], 2),    # varying f-block size (schur_eliminator_test.cc:262-330)
+    (2, [1, 5, 3, 3], 0),       # every size dynamic
+    (5, [2, 2, 2], 3),          # e blocks of 5: InvertPSDMatrix takes the Cholesky route (invert_psd_matrix.h:60-72)
+])
+@pytest.mark.parametrize("threads", [1, 4])
+def test_explicit_and_implicit_oracle_on_random_block_structures(shape, threads):
+    e_size, f_sizes, row_size = shape
+    for seed in range(4):
+        st, values, b, D = _random_schur_problem(seed, e_size, f_sizes, row_size)
+        A = st.dense(values)
+        ne = st.num_cols_e
+        S = dense_schur(A, D, ne)
+        ref = dense_solution(A, b, D)
+        o = ob.Oracle(st, num_threads=threads, preconditioner_type=ob.SCHUR_JACOBI,
+                      max_num_iterations=4 * st.num_cols_f)
+        row_ptr, cols, pos, vals, rhs = o.explicit_eliminate(values, b, D)
+        got = _dense_from_upper(row_ptr, cols, pos, vals, st.col_size[st.num_eliminate_blocks:])
+        # pairs that no row produces are not stored; the dense S is exactly zero there
+        np.testing.assert_allclose(got, S, atol=1e-12 * np.abs(S).max())
+        x, s = o.explicit_solve(values, b, D, q_tolerance=-1.0, r_tolerance=1e-13)
+        assert ob.TERMINATION[s["termination_type"]] == "SUCCESS", s
+        assert np.linalg.norm(x - ref) < 1e-10 * np.linalg.norm(ref)
+        xi, si = o.solve(values, b, D, q_tolerance=-1.0, r_tolerance=1e-13)
+        assert np.linalg.norm(xi - ref) < 1e-10 * np.linalg.norm(ref)
+        o.isc_init(values, D, b)
+        v = np.random.default_rng(seed).standard_normal(st.num_cols_f)
+        np.testing.assert_allclose(o.isc_multiply(v), S @ v, atol=1e-12 * np.abs(S).max() * np.abs(v).sum())
