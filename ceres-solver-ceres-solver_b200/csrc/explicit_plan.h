@@ -12,11 +12,24 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <thread>
 #include <vector>
 
 #include "flatten.h"
 
 namespace cb200 {
+
+// fn(thread, begin, end) over [0, n) cut into contiguous ranges, one host thread each (planning is
+// once per solver lifetime, but 2 x 21 M pairs at Venice shape are seconds on one core).
+template <typename Fn>
+inline void ParallelRanges(int n, Fn fn) {
+  const int nt = std::max(1, std::min<int>({(int)std::thread::hardware_concurrency(), 16, n / 1024 + 1}));
+  if (nt == 1) { fn(0, 0, n); return; }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nt; ++t)
+    pool.emplace_back(fn, t, (int)((long long)n * t / nt), (int)((long long)n * (t + 1) / nt));
+  for (auto& th : pool) th.join();
+}
 
 constexpr int kFormRows = 16;  // rows of one point whose outer products one warp item owns
 
@@ -48,21 +61,27 @@ inline ExplicitStructure PlanExplicitStructure(const FlatStructure& flat) {
   for (int p = 0; p < P; ++p)
     for (int r = flat.point_row_start[p]; r < flat.point_row_start[p + 1]; ++r) row_point[r] = p;
   for (int r = 0; r < flat.num_obs; ++r) cam_rows[cursor[flat.cam_idx[r]]++] = r;
-  std::vector<int> mark(C, -1), row_cols;
+  // columns of every block row (independent per row: camera ranges on host threads)
+  std::vector<std::vector<int>> cols_of(C);
+  ParallelRanges(C, [&](int, int c_begin, int c_end) {
+    std::vector<int> mark(C, -1);
+    for (int i = c_begin; i < c_end; ++i) {
+      std::vector<int>& row_cols = cols_of[i];
+      mark[i] = i;
+      row_cols.push_back(i);  // the diagonal pair always exists (:233-235)
+      for (int k = cam_start[i]; k < cam_start[i + 1]; ++k) {
+        const int p = row_point[cam_rows[k]];
+        for (int r = flat.point_row_start[p]; r < flat.point_row_start[p + 1]; ++r) {
+          const int j = flat.cam_idx[r];
+          if (j > i && mark[j] != i) { mark[j] = i; row_cols.push_back(j); }
+        }
+      }
+      std::sort(row_cols.begin(), row_cols.end());
+    }
+  });
   es.row_ptr.assign(C + 1, 0);
   for (int i = 0; i < C; ++i) {
-    row_cols.clear();
-    mark[i] = i;
-    row_cols.push_back(i);  // the diagonal pair always exists (:233-235)
-    for (int k = cam_start[i]; k < cam_start[i + 1]; ++k) {
-      const int p = row_point[cam_rows[k]];
-      for (int r = flat.point_row_start[p]; r < flat.point_row_start[p + 1]; ++r) {
-        const int j = flat.cam_idx[r];
-        if (j > i && mark[j] != i) { mark[j] = i; row_cols.push_back(j); }
-      }
-    }
-    std::sort(row_cols.begin(), row_cols.end());
-    es.col.insert(es.col.end(), row_cols.begin(), row_cols.end());
+    es.col.insert(es.col.end(), cols_of[i].begin(), cols_of[i].end());
     es.row_ptr[i + 1] = (int)es.col.size();
   }
   es.t_ptr.assign(C + 1, 0);
@@ -107,26 +126,29 @@ inline ExplicitFormPlan PlanExplicitForm(const ExplicitStructure& es, const int*
     plan.pair_start[p + 1] = plan.pair_start[p] + k * (k + 1) / 2;
   }
   plan.pair_cell.resize((size_t)plan.pair_start[P_loc]);
-  for (int p = 0; p < P_loc; ++p) {
-    const int r0 = row_start[p], k = row_start[p + 1] - r0;
-    for (int u = 0; u < k; ++u) plan.srow[r0 + u] = r0 + u;
-    std::stable_sort(plan.srow.begin() + r0, plan.srow.begin() + r0 + k,
-                     [&](int a, int b) { return cam[a] < cam[b]; });
-    size_t out = (size_t)plan.pair_start[p];
-    for (int u = 0; u < k; ++u) {
-      const int ci = cam[plan.srow[r0 + u]];
-      const int* first = es.col.data() + es.row_ptr[ci];
-      const int* last = es.col.data() + es.row_ptr[ci + 1];
-      for (int v = u; v < k; ++v) {
-        const int cj = cam[plan.srow[r0 + v]];
-        first = std::lower_bound(first, last, cj);  // cj ascends with v: resume where the last search ended
-        unsigned int cell = (unsigned int)(first - es.col.data());
-        if (v > u && cj == ci) cell |= kFormDuplicate;
-        plan.pair_cell[out++] = cell;
+  ParallelRanges(P_loc, [&](int, int p_begin, int p_end) {
+    for (int p = p_begin; p < p_end; ++p) {
+      const int r0 = row_start[p], k = row_start[p + 1] - r0;
+      for (int u = 0; u < k; ++u) plan.srow[r0 + u] = r0 + u;
+      std::stable_sort(plan.srow.begin() + r0, plan.srow.begin() + r0 + k,
+                       [&](int a, int b) { return cam[a] < cam[b]; });
+      size_t out = (size_t)plan.pair_start[p];
+      for (int u = 0; u < k; ++u) {
+        const int ci = cam[plan.srow[r0 + u]];
+        const int* first = es.col.data() + es.row_ptr[ci];
+        const int* last = es.col.data() + es.row_ptr[ci + 1];
+        for (int v = u; v < k; ++v) {
+          const int cj = cam[plan.srow[r0 + v]];
+          first = std::lower_bound(first, last, cj);  // cj ascends with v: resume where the last search ended
+          unsigned int cell = (unsigned int)(first - es.col.data());
+          if (v > u && cj == ci) cell |= kFormDuplicate;
+          plan.pair_cell[out++] = cell;
+        }
       }
     }
-    for (int u0 = 0; u0 < k; u0 += kFormRows) plan.items.push_back(FormItem{p, u0});
-  }
+  });
+  for (int p = 0; p < P_loc; ++p)
+    for (int u0 = 0; u0 < row_start[p + 1] - row_start[p]; u0 += kFormRows) plan.items.push_back(FormItem{p, u0});
   // Order of execution. The cells a point touches lie in the block rows of its cameras, and S is 2-3x
   // the L2 at Ladybug / Venice shape: in point order (random home cameras) every reduction into it
   // missed (11 GB of DRAM traffic for 1.3 GB of data at Venice). So items are grouped by their point's
