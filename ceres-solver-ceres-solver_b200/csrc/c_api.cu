@@ -199,6 +199,12 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     return Fail(CB200_ERR_INVALID_ARGUMENT, "world_size > 1 needs nccl_unique_id");
   if (o.residual_reset_period <= 0 || o.max_num_iterations < 0 || o.min_num_iterations < 0)
     return Fail(CB200_ERR_INVALID_ARGUMENT, "bad iteration options");
+  if (o.explicit_switch_iterations < 0 ||
+      (o.explicit_switch_iterations > 0 &&
+       (o.world_size != 1 || o.preconditioner_type == CB200_SCHUR_POWER_SERIES_EXPANSION ||
+        o.use_spse_initialization)))
+    return Fail(CB200_ERR_INVALID_ARGUMENT,
+                "explicit_switch_iterations needs one GPU, a block-diagonal preconditioner and no SPSE initialisation");
   if (o.use_explicit_schur_complement) {  // solver.cc:277-290
     if (o.preconditioner_type != CB200_SCHUR_JACOBI)
       return Fail(CB200_ERR_INVALID_ARGUMENT,
@@ -406,7 +412,7 @@ int cb200_create(const cb200_structure* structure, const cb200_options* options,
     TRY_CUDA(cudaMemcpy(&ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost));
     s->peer_allreduce = (ok == (double)o.world_size);
   }
-  if (o.use_explicit_schur_complement) {
+  if (o.use_explicit_schur_complement || o.explicit_switch_iterations > 0) {
     // block structure of S from the GLOBAL problem (identical on every rank), destinations of
     // this shard's outer products
     const ExplicitStructure es = PlanExplicitStructure(flat);

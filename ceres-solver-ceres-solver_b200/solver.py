@@ -33,7 +33,8 @@ class COptions(ctypes.Structure):
                 ("max_num_spse_iterations", ctypes.c_int), ("spse_tolerance", ctypes.c_double),
                 ("device_id", ctypes.c_int), ("rank", ctypes.c_int), ("world_size", ctypes.c_int),
                 ("nccl_unique_id", ctypes.c_char_p), ("y_replicas", ctypes.c_int),
-                ("status_check_period", ctypes.c_int), ("use_explicit_schur_complement", ctypes.c_int)]
+                ("status_check_period", ctypes.c_int), ("use_explicit_schur_complement", ctypes.c_int),
+                ("explicit_switch_iterations", ctypes.c_int)]
 
 
 class CSummary(ctypes.Structure):
@@ -250,14 +251,15 @@ class IterativeSchurComplementSolver:
                  max_num_iterations=500, residual_reset_period=10, use_spse_initialization=False,
                  max_num_spse_iterations=5, spse_tolerance=0.1, device_id=0, rank=0, world_size=1,
                  nccl_unique_id=None, y_replicas=0, status_check_period=0,
-                 use_explicit_schur_complement=False):
+                 use_explicit_schur_complement=False, explicit_switch_iterations=0):
         self.L = lib()
         self.structure = structure
         cs = structure.c_struct()
         opt = COptions(structure.num_eliminate_blocks, preconditioner_type, min_num_iterations,
                        max_num_iterations, residual_reset_period, int(use_spse_initialization),
                        max_num_spse_iterations, spse_tolerance, device_id, rank, world_size,
-                       nccl_unique_id, y_replicas, status_check_period, int(use_explicit_schur_complement))
+                       nccl_unique_id, y_replicas, status_check_period, int(use_explicit_schur_complement),
+                       explicit_switch_iterations)
         h = _H()
         _check(self.L.cb200_create(ctypes.byref(cs), ctypes.byref(opt), ctypes.byref(h)))
         self.h = h

@@ -95,6 +95,13 @@ typedef struct cb200_options {
                                  SolveReducedLinearSystemUsingConjugateGradients,
                                  schur_complement_solver.cc:337-408). SCHUR_JACOBI only,
                                  no SPSE initialisation (solver.cc:277-290).          */
+  int explicit_switch_iterations; /* 0 = never (default). n > 0 (one GPU, IDENTITY / JACOBI /
+                                 SCHUR_JACOBI): a solve on the implicit operator that is
+                                 still running after n PCG iterations forms the explicit
+                                 matrix once and continues THE SAME iteration on it (same
+                                 operator, same preconditioner, same vectors; products
+                                 agree to 1e-12). Not a reference option: an internal
+                                 speed-up for long solves.              */
 } cb200_options;
 
 /* LinearSolver::Summary (linear_solver.h:320-326) + per-phase device timings. */

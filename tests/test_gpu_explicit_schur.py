@@ -207,3 +207,28 @@ def test_explicit_seams_report_call_order_errors():
     ge.upload(values)                                    # new values invalidate the matrix
     with pytest.raises(m.B200Error, match="error -5"):
         ge.explicit_multiply(np.zeros(st.num_cols_f))
+
+
+@pytest.mark.parametrize("switch_at,period", [(4, 4), (1, 1), (8, 3)])
+def test_switch_to_explicit_matrix_mid_solve_keeps_the_iterates(switch_at, period):
+    """explicit_switch_iterations: the implicit solve forms the explicit matrix after `switch_at` iterations
+    and continues the same PCG on it. Same operator, so every iterate, the iteration count, the
+    termination and the solution still match the oracle's IMPLICIT solver within the usual bars."""
+    from tests.test_gpu_parity import compare_solve as compare_implicit
+    m, st, values, b, D = long_point_problem()
+    _, sg, _ = compare_implicit(m, st, values, b, D, "SCHUR_JACOBI", r_tol=1e-9, max_it=300, check_period=period,
+                                explicit_switch_iterations=switch_at)
+    assert sg["num_iterations"] > 12  # ran on both operators, across a residual reset on the explicit one
+    m2 = util.pkg()
+    p = m2.SyntheticBAL.named("ladybug", scale=0.05)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    for ptype in ("SCHUR_JACOBI", "JACOBI"):
+        compare_implicit(m2, p.structure, values, residuals, D, ptype, q_tol=1e-3, r_tol=-1.0, max_it=300,
+                         check_period=period, explicit_switch_iterations=switch_at)
+
+
+def test_switch_option_validation():
+    m, st, values, b, D = problem()
+    with pytest.raises(m.B200Error, match="explicit_switch_iterations"):
+        m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_POWER_SERIES_EXPANSION,
+                                         explicit_switch_iterations=5)
