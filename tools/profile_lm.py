@@ -18,11 +18,13 @@ def main():
     ap.add_argument("--eta", type=float, default=1e-2)
     ap.add_argument("--repeat", type=int, default=2)
     ap.add_argument("--explicit", action="store_true", help="use_explicit_schur_complement")
+    ap.add_argument("--switch", type=int, default=0, help="explicit_switch_iterations")
     args = ap.parse_args()
     pkg = importlib.import_module("ceres-solver-ceres-solver_b200")
     p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
     g = pkg.IterativeSchurComplementSolver(p.structure, max_num_iterations=500,
-                                           use_explicit_schur_complement=args.explicit)
+                                           use_explicit_schur_complement=args.explicit,
+                                           explicit_switch_iterations=args.switch)
     g.bal_attach(p.observations)
     for _ in range(args.repeat):
         g.bal_set_parameters(p.cameras, p.points)
