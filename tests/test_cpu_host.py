@@ -134,3 +134,27 @@ def test_explicit_schur_option_validation():
     with pytest.raises(m.B200Error, match="does not support use_spse_initialization"):
         m.IterativeSchurComplementSolver(p.structure, use_spse_initialization=True,
                                          use_explicit_schur_complement=True)
+
+
+def build_adapter_class_driver(tmp_path):
+    import subprocess
+    m = util.pkg()
+    lib = m._build.build_cuda()
+    exe = str(tmp_path / "adapter_class_driver")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I" + os.path.join(util.ROOT, "tests", "cpp", "standin_ceres"),
+                    "-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_class_driver.cc"), lib,
+                    "-Wl,-rpath," + os.path.dirname(lib)], check=True)
+    return exe
+
+
+@pytest.mark.skipif(util.has_gpu(), reason="needs a machine without a GPU")
+def test_adapter_class_compiles_and_reports_fatal_error_without_a_gpu(tmp_path):
+    """B200IterativeSchurComplementSolver (include/ceres_b200_adapter.h, the class INTEGRATION.md adds to
+    linear_solver.cc) compiled against stand-ins for linear_solver.h / block_sparse_matrix.h and driven
+    through LinearSolver::Solve: without a device it must come back with FATAL_ERROR and the library's
+    message, never fall back to a CPU path."""
+    import subprocess
+    exe = build_adapter_class_driver(tmp_path)
+    for mode in ("i", "e"):
+        out = subprocess.run([exe, mode], check=True, capture_output=True, text=True).stdout
+        assert "termination=3" in out and "no CUDA device" in out, out

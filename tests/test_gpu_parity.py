@@ -479,3 +479,16 @@ def test_host_registered_buffers_upload_faster_and_solve_the_same():
     assert s1["num_iterations"] == s0["num_iterations"] and util.rel_err(x1, x0) < 1e-11  # (atomics: not bitwise)
     assert s1["h2d_ms"] <= 1.05 * s0["h2d_ms"], (s0["h2d_ms"], s1["h2d_ms"])
     g.close()
+
+
+@pytest.mark.parametrize("mode", ["implicit", "explicit"])
+def test_adapter_class_solves_through_linear_solver_interface(tmp_path, mode):
+    """The Ceres-side adapter class (include/ceres_b200_adapter.h) driven through LinearSolver::Solve on a
+    BlockSparseMatrix stand-in: SUCCESS, and x solves the normal equations (J'J + D^2) x = J'b."""
+    import subprocess
+    from tests.test_cpu_host import build_adapter_class_driver
+    exe = build_adapter_class_driver(tmp_path)
+    out = subprocess.run([exe, mode[0]], check=True, capture_output=True, text=True, timeout=120).stdout
+    kv = dict(t.split("=", 1) for t in out.split() if "=" in t)
+    assert kv["termination"] == "0", out
+    assert 0 < int(kv["iterations"]) <= 100 and 0.0 <= float(kv["residual"]) < 1e-8, out
