@@ -158,3 +158,19 @@ def test_adapter_class_compiles_and_reports_fatal_error_without_a_gpu(tmp_path):
     for mode in ("i", "e"):
         out = subprocess.run([exe, mode], check=True, capture_output=True, text=True).stdout
         assert "termination=3" in out and "no CUDA device" in out, out
+
+
+def test_explicit_plan_invariants_host_only(tmp_path):
+    """csrc/explicit_plan.h on a random structure with unsorted cameras, duplicate (point, camera) rows, empty
+    points and 40-row points: block pairs == InitStorage's set, column lists cover every strictly-upper cell
+    once, every (u <= v) pair of every point lands in the cell (camera u, camera v) with the duplicate flag
+    exactly where two rows share a camera, and the work items cover every 16-row chunk once."""
+    import subprocess
+    exe = str(tmp_path / "explicit_plan_driver")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", "-o", exe,
+                    os.path.join(util.ROOT, "tests", "cpp", "explicit_plan_driver.cc")], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
+    kv = dict(t.split("=") for t in out.split())
+    assert int(kv["cells"]) > 37 and int(kv["dup_pairs"]) > 0 and int(kv["items"]) > 400, out
+    for k in ("bad_structure", "bad_transpose", "bad_pairs", "bad_order", "bad_items"):
+        assert kv[k] == "0", out
