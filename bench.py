@@ -438,7 +438,7 @@ def cpu_baseline(p, values, residuals, D, precond):
     from oracle import lm_reference as lmr
     t0 = time.perf_counter()
     r = lmr.minimize(p, p.cameras, p.points, lambda v, b, Dv, e: o.solve(v, b, Dv, e, -1.0), eta=ETA,
-                     max_num_iterations=2, initial_trust_region_radius=RADIUS)
+                     max_num_iterations=2, initial_trust_region_radius=RADIUS, independent_evaluator=False)
     dt = time.perf_counter() - t0
     n_it = len(r["iterations"]) - 1
     out["lm_loop"] = {"lm_iterations": n_it, "lm_iters_per_sec": n_it / dt, "final_cost": r["final_cost"],

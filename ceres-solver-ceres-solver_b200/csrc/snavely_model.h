@@ -93,13 +93,29 @@ CB200_HD double Sqrt(double a) { return sqrt(a); }
 CB200_HD double Sin(double a) { return sin(a); }
 CB200_HD double Cos(double a) { return cos(a); }
 
-// Rodrigues rotation of pt by the angle-axis vector aa, with the first-order
-// branch near zero so derivatives stay finite (rotation.h:792-850).
+// hypot(x, y, z) of three scalars / dual numbers (jet.h: value std::hypot, partials x/h dx + y/h dy + z/h dz).
+CB200_HD double Hypot3(double x, double y, double z) {
+#ifdef __CUDA_ARCH__
+  return norm3d(x, y, z);
+#else
+  return std::hypot(x, y, z);
+#endif
+}
+template <int N> CB200_HD DualN<N> Hypot3(const DualN<N>& x, const DualN<N>& y, const DualN<N>& z) {
+  DualN<N> r; r.v = Hypot3(x.v, y.v, z.v);
+  const double ax = x.v / r.v, ay = y.v / r.v, az = z.v / r.v;
+#pragma unroll
+  for (int i = 0; i < N; ++i) r.d[i] = ax * x.d[i] + ay * y.d[i] + az * z.d[i];
+  return r;
+}
+
+// Rodrigues rotation of pt by the angle-axis vector aa (rotation.h:792-850). As in the
+// reference, the first-order branch is taken only when theta = hypot(aa) is EXACTLY zero
+// (:799-801, fpclassify(theta) != FP_ZERO): it exists to give finite derivatives there.
 template <typename T>
 CB200_HD void RotateByAngleAxis(const T* aa, const T* pt, T* out) {
-  const T theta2 = aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2];
-  if (Val(theta2) > 2.220446049250313e-16) {
-    const T theta = Sqrt(theta2);
+  if (Hypot3(Val(aa[0]), Val(aa[1]), Val(aa[2])) != 0.0) {
+    const T theta = Hypot3(aa[0], aa[1], aa[2]);
     const T c = Cos(theta), s = Sin(theta);
     const T inv = Lift<T>(1.0) / theta;
     const T w[3] = {aa[0] * inv, aa[1] * inv, aa[2] * inv};

@@ -13,9 +13,12 @@ ITERATIVE_SCHUR solve, for the final-cost parity statement of BASELINE.json's no
   BlockSparseMatrix::SquaredColumnNorm / ScaleColumns   internal/ceres/block_sparse_matrix.cc:351-450
 
 Monotonic steps, no bounds, no inner iterations (what examples/bundle_adjuster.cc runs by default).
-The problem object supplies evaluate / squared_column_norm / scale_columns / jacobian_times
-(the host evaluator of the synthetic BAL problems); linear_solve(values, residuals, D, eta) returns
-(y, summary) for J y = r.
+The residuals, the Jacobian, the column norms / scaling and J*step come from oracle/snavely_reference.py
+(ReferenceProblem: numpy restatement of SnavelyReprojectionError + Jet autodiff, no product code);
+only the problem's DATA (structure, observations, parameters) is taken from the object passed in.
+independent_evaluator=False keeps the object's own evaluate / squared_column_norm / scale_columns /
+jacobian_times instead (bench.py's CPU timing leg, where the product's OpenMP host evaluator is only a
+faster clock, not a checker). linear_solve(values, residuals, D, eta) returns (y, summary) for J y = r.
 """
 import numpy as np
 
@@ -25,9 +28,12 @@ DEFAULTS = dict(max_num_iterations=50, initial_trust_region_radius=1e4, max_trus
                 parameter_tolerance=1e-8, jacobi_scaling=True, max_num_consecutive_invalid_steps=5)
 
 
-def minimize(problem, cameras, points, linear_solve, **options):
+def minimize(problem, cameras, points, linear_solve, independent_evaluator=True, **options):
     o = dict(DEFAULTS)
     o.update(options)
+    if independent_evaluator:
+        from oracle.snavely_reference import ReferenceProblem
+        problem = ReferenceProblem.of(problem)
     P = problem.P
     x = np.concatenate([points, cameras]).astype(np.float64)  # column order of the Jacobian: points, cameras
     split = lambda v: (v[3 * P:], v[:3 * P])  # -> cameras, points

@@ -356,3 +356,94 @@ def test_explicit_and_implicit_oracle_on_random_block_structures(shape, threads)
         o.isc_init(values, D, b)
         v = np.random.default_rng(seed).standard_normal(st.num_cols_f)
         np.testing.assert_allclose(o.isc_multiply(v), S @ v, atol=1e-12 * np.abs(S).max() * np.abs(v).sum())
+
+
+# ---- the independent Snavely / Jet restatement (oracle/snavely_reference.py) --------------------------
+# Pins the evaluator oracle WITHOUT any product code: hand-computed projections, complex-step derivatives
+# of the plain residual, and the exact-zero switch of AngleAxisRotatePoint (rotation.h:799-801).
+
+def test_snavely_reference_known_answers():
+    from oracle import snavely_reference as sr
+    # aa = 0 (Taylor branch, R = I): p = X + t = (0.1, 0.2, -2); xp = 0.05, yp = 0.1, r2 = 0.0125;
+    # distortion = 1 + 0.0125 (0.1 + 0.01 * 0.0125) = 1.0012515625; f = 100 -> (5.0062578125, 10.012515625)
+    cam = np.array([[0, 0, 0, 0, 0, 0, 100.0, 0.1, 0.01]])
+    rx, ry = sr.snavely_residual_jets(cam, np.array([[0.1, 0.2, -2.0]]), np.zeros((1, 2)))
+    assert abs(rx.a[0] - 5.0062578125) < 1e-14 and abs(ry.a[0] - 10.012515625) < 1e-14
+    # rotation by pi/2 about z maps (0.2, -0.1, -2) to (0.1, 0.2, -2): the same image point
+    cam2 = cam.copy()
+    cam2[0, 2] = np.pi / 2
+    rx2, ry2 = sr.snavely_residual_jets(cam2, np.array([[0.2, -0.1, -2.0]]), np.zeros((1, 2)))
+    assert abs(rx2.a[0] - 5.0062578125) < 1e-13 and abs(ry2.a[0] - 10.012515625) < 1e-13
+    # translation and observation enter linearly: t_z = -1 with X_z = -1 gives the same depth
+    cam3 = cam.copy()
+    cam3[0, 5] = -1.0
+    rx3, ry3 = sr.snavely_residual_jets(cam3, np.array([[0.1, 0.2, -1.0]]), np.array([[5.0, 10.0]]))
+    assert abs(rx3.a[0] - 0.0062578125) < 1e-13 and abs(ry3.a[0] - 0.012515625) < 1e-13
+    # d pred_x / d focal = distortion * xp, by hand
+    assert abs(rx.v[0, 6] - 1.0012515625 * 0.05) < 1e-15
+
+
+def test_snavely_reference_jets_match_complex_step():
+    from oracle import snavely_reference as sr
+    rng = np.random.default_rng(5)
+    n = 200
+    cam = np.concatenate([0.3 * rng.standard_normal((n, 3)), rng.standard_normal((n, 3)),
+                          rng.uniform(500, 1500, (n, 1)), 1e-2 * rng.standard_normal((n, 2))], axis=1)
+    pt = rng.standard_normal((n, 3))
+    pt[:, 2] -= 6.0
+    obs = rng.standard_normal((n, 2))
+    rx, ry = sr.snavely_residual_jets(cam, pt, obs)
+    plain = sr.snavely_residual_plain(cam, pt, obs)
+    assert np.abs(plain[:, 0] - rx.a).max() < 1e-10 and np.abs(plain[:, 1] - ry.a).max() < 1e-10
+    h = 1e-30
+    for k in range(12):
+        c, x = cam.astype(complex), pt.astype(complex)
+        if k < 9:
+            c[:, k] += 1j * h
+        else:
+            x[:, k - 9] += 1j * h
+        d = sr.snavely_residual_plain(c, x, obs).imag / h
+        scale = max(1.0, np.abs(d).max())
+        assert np.abs(d[:, 0] - rx.v[:, k]).max() < 1e-11 * scale, k
+        assert np.abs(d[:, 1] - ry.v[:, k]).max() < 1e-11 * scale, k
+
+
+def test_snavely_reference_zero_rotation_branch_is_exact_zero_only():
+    """rotation.h:799-801 switches on fpclassify(theta) != FP_ZERO: |aa| = 1e-9 still takes Rodrigues."""
+    from oracle import snavely_reference as sr
+    base = np.array([[0, 0, 0, 0.1, -0.2, 0.3, 800.0, 1e-3, 1e-4]])
+    pt, obs = np.array([[0.4, -0.3, -5.0]]), np.zeros((1, 2))
+    rx0, ry0 = sr.snavely_residual_jets(base, pt, obs)
+    assert np.all(np.isfinite(rx0.v)) and np.all(np.isfinite(ry0.v))
+    # at exactly zero: d p / d aa = -hat(pt) (first-order branch)
+    tiny = base.copy()
+    tiny[0, 0:3] = [6e-10, -5e-10, 4e-10]
+    rx1, ry1 = sr.snavely_residual_jets(tiny, pt, obs)
+    assert abs(rx1.a[0] - rx0.a[0]) < 1e-6 and np.abs(rx1.v - rx0.v).max() < 1e-5 * np.abs(rx0.v).max()
+    c, x = tiny.astype(complex), pt.astype(complex)
+    c[0, 1] += 1e-30j
+    d = sr.snavely_residual_plain(c, x, obs).imag / 1e-30
+    assert abs(d[0, 0] - rx1.v[0, 1]) < 1e-6 * abs(d[0, 0])
+
+
+@pytest.mark.parametrize("zero_cameras", [False, True])
+def test_host_evaluator_matches_snavely_reference(zero_cameras):
+    """The product's host evaluator (csrc/synthetic_bal.cc + csrc/snavely_model.h, the code the device
+    kernel shares) against the independent restatement: residuals, cost and every Jacobian block."""
+    from oracle import snavely_reference as sr
+    from tests import util
+    m = util.pkg()
+    p = m.SyntheticBAL(12, 400, 1700, seed=9)
+    cams = p.cameras.copy()
+    if zero_cameras:  # exact-zero and tiny rotations: both branches of AngleAxisRotatePoint
+        c = cams.reshape(-1, 9)
+        c[0, 0:3] = 0.0
+        c[1, 0:3] = [3e-9, -2e-9, 1e-9]
+    cost, residuals, values = p.evaluate(cameras=cams)
+    rcost, rres, rvalues = sr.evaluate(p.point_row_start, p.cam_idx, p.observations, cams, p.points)
+    assert abs(cost - rcost) <= 1e-13 * rcost
+    assert util.rel_err(residuals, rres) < 1e-13
+    # per-block comparison: tiny-rotation blocks carry 1/theta cancellation, so compare column-wise at 1e-7
+    assert util.rel_err(values, rvalues) < (1e-7 if zero_cameras else 1e-12)
+    c2, r2, _ = sr.evaluate(p.point_row_start, p.cam_idx, p.observations, cams, p.points, jacobian=False)
+    assert abs(c2 - rcost) <= 1e-13 * rcost and util.rel_err(r2, rres) < 1e-13
