@@ -146,6 +146,60 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
   }
 }
 
+// Deterministic mode (cb200_options::deterministic): y_c = sum over the rows r of camera c of F_r' w_r, the
+// camera scatter of a point pass (LeftMultiplyAndAccumulateF, partitioned_matrix_view_impl.h:266-375, whose
+// multi-threaded form also walks the rows camera by camera) summed in a FIXED order instead of with FP64
+// atomics: thread t of the chunk's CTA takes rows t, t + 128, ... in order, then a fixed shuffle / shared-memory
+// tree. Same chunks as camera_block_kernel; out: 9 sums per chunk, folded per camera by
+// camera_gather_finish_kernel. A repeatability option, not the fast path: F is gathered camera-major.
+__global__ void __launch_bounds__(kChunkThreads)
+camera_gather_kernel(const int* done, const double* __restrict__ F, const double* __restrict__ w_rows,
+                     const int* __restrict__ cam_perm, const int* __restrict__ chunk_begin,
+                     double* __restrict__ chunk_partial9) {
+  if (done != nullptr && *done) return;
+  __shared__ double sred[kChunkThreads / 32][9];
+  const int begin = chunk_begin[blockIdx.x], end = chunk_begin[blockIdx.x + 1];
+  double acc[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) acc[k] = 0.0;
+  for (int i = begin + threadIdx.x; i < end; i += kChunkThreads) {
+    const int r = __ldg(cam_perm + i);
+    const double2 w = reinterpret_cast<const double2*>(w_rows)[r];
+    const double2* f2 = reinterpret_cast<const double2*>(F + (size_t)r * 18);
+    double f[18];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { const double2 v = f2[k]; f[2 * k] = v.x; f[2 * k + 1] = v.y; }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) acc[k] += f[k] * w.x + f[9 + k] * w.y;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0) sred[warp][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 9) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < kChunkThreads / 32; ++w) s += sred[w][threadIdx.x];
+    chunk_partial9[(size_t)blockIdx.x * 9 + threadIdx.x] = s;
+  }
+}
+__global__ void __launch_bounds__(256)
+camera_gather_finish_kernel(const int* done, const double* __restrict__ chunk_partial9,
+                            const int* __restrict__ cam_chunk_start, int C, double* __restrict__ out /* 9C */) {
+  if (done != nullptr && *done) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 9 * C) return;
+  const int c = i / 9, k = i - 9 * c;
+  double s = 0.0;
+  for (int ch = cam_chunk_start[c]; ch < cam_chunk_start[c + 1]; ++ch) s += chunk_partial9[(size_t)ch * 9 + k];
+  out[i] = s;
+}
+
 // Cross terms of two rows (ri != rj) of the same point that see the same camera
 // (the eliminator merges them in its per-camera buffer before the outer product,
 // schur_eliminator_impl.h:140-148,491-501): S_cc -= F_i' E_i c E_j' F_j + transpose.
@@ -154,8 +208,8 @@ __global__ void duplicate_pair_kernel(const double* __restrict__ E, const double
                                       const int* __restrict__ cam, const int* __restrict__ row_start,
                                       const double* __restrict__ De, const int* __restrict__ pairs,
                                       int num_pairs, double* __restrict__ dup_blocks) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= num_pairs) return;
+  // (grid-stride: deterministic mode runs the whole list on ONE thread so the additions keep their order)
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < num_pairs; t += gridDim.x * blockDim.x) {
   const int p = pairs[3 * t], ri = pairs[3 * t + 1], rj = pairs[3 * t + 2];
   double m[9];
   for (int k = 0; k < 9; ++k) m[k] = 0.0;
@@ -186,6 +240,7 @@ __global__ void duplicate_pair_kernel(const double* __restrict__ E, const double
       const double v2 = fj[a] * (X[0] * fi[b] + X[2] * fi[9 + b]) + fj[9 + a] * (X[1] * fi[b] + X[3] * fi[9 + b]);
       atomicAdd(out + a * 9 + b, -(v1 + v2));
     }
+  }
 }
 
 // Sum the chunk partials of each camera in chunk order, add D_c^2 (and the

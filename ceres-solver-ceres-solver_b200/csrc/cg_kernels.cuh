@@ -16,7 +16,12 @@
 namespace cb200 {
 
 constexpr int kVecThreads = 256;
-constexpr int kMaxVecBlocks = 1024;
+constexpr int kMaxVecBlocks = 1024;    // CTAs of the stand-alone vector kernels (their last CTA sums the partials alone)
+constexpr int kMaxStepBlocks = 4096;   // CTAs of the fused step kernel (14 cameras each: up to 57 344 cameras)
+// PCG iterations whose per-point intermediate v_k = (E'E + D_e^2)^-1 E'F p_k is kept, so that a solve
+// that ends within this many iterations gets its back substitution as y_e = v_rhs - sum alpha_k v_k
+// (a 3P-sized combination) instead of one more pass over the Jacobian (stream_kernels.cuh).
+constexpr int kHistCap = 8;
 
 // message selectors (host formats the reference's strings from these)
 enum CgReason {
@@ -41,10 +46,21 @@ struct CgState {
   int reason;                  // CgReason
   int min_iterations, max_iterations;
   int peer_timeout;            // a peer's partial sum never arrived (cg_step.cuh); fatal
-  unsigned int ticket[5];            // [4]: peer_publish_kernel
+  int hist_valid;              // 1: every x update so far has its alpha in alpha_hist (and its v_k stored)
+  double alpha_hist[kHistCap]; // step lengths of iterations 1 .. kHistCap (0 where x was not updated)
+  unsigned long long stamp[4]; // %globaltimer at: solve start, PCG start, PCG end (= done), spare
+  // ---- everything above is the "head": reset from the host at the start of a solve, read back after ----
+  unsigned int ticket[12];           // [0..3] FinishDots; [4 + 2c], [5 + 2c]: peer_allreduce_kernel on channel c
   unsigned int bar_count, bar_flag;  // grid barrier of cg_step_kernel: arrivals (0 between launches), barriers completed
-  double partial[6][kMaxVecBlocks];
+  unsigned int peer_epoch[2];        // exchanges completed on peer channel 0 (main stream) / 1 (side stream)
+  double partial[6][kMaxStepBlocks];
 };
+
+__device__ __forceinline__ unsigned long long GlobalTimerNs() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
 __device__ __forceinline__ bool IsZeroOrInfinity(double x) { return x == 0.0 || isinf(x); }
 
@@ -81,6 +97,7 @@ __device__ __forceinline__ bool FinishDots(CgState* st, int slot, const double* 
 __device__ __forceinline__ void Finish(CgState* st, int termination, int reason) {
   st->termination = termination;
   st->reason = reason;
+  st->stamp[2] = GlobalTimerNs();
   st->done = 1;
 }
 
@@ -107,6 +124,7 @@ cg_begin_kernel(CgState* st, const double* __restrict__ rhs, const double* __res
     st->norm_r = sqrt(sums[1]);
     st->rho = 1.0;
     st->Q0 = -sums[2];
+    st->stamp[1] = GlobalTimerNs();
     if (st->norm_rhs == 0.0) {
       Finish(st, CB200_LINEAR_SOLVER_SUCCESS, kReasonZeroRhs);
     } else if (st->min_iterations == 0 && st->norm_r <= st->tol_r) {
@@ -224,7 +242,8 @@ cg_pq_kernel(CgState* st, const double* __restrict__ Df, const double* __restric
       return;
     }
     st->alpha = st->rho / st->pq;
-    if (isinf(st->alpha)) Finish(st, CB200_LINEAR_SOLVER_FAILURE, kReasonAlphaFailure);
+    if (isinf(st->alpha)) { Finish(st, CB200_LINEAR_SOLVER_FAILURE, kReasonAlphaFailure); return; }
+    if (st->iter <= kHistCap) st->alpha_hist[st->iter - 1] = st->alpha;  // x += alpha p follows
   }
 }
 

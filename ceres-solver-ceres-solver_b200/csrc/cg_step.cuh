@@ -46,7 +46,10 @@ struct CgStepArgs {
   // several GPUs, fused all-reduce over NVLink peer memory: every rank publishes its folded
   // partial in its own buffer (two slots, alternating) and reads all ranks' in rank order
   int world, rank;
-  unsigned int epoch;            // value this launch writes to / expects in the flags
+  unsigned int* epoch;           // device counter of exchanges completed on this channel (CgState::peer_epoch):
+                                 // this launch's exchange is number *epoch + 1, written back by CTA 0 -- kept
+                                 // on the device so that launches replayed from a CUDA graph, and launches that
+                                 // return early because the solve is over, stay in step on every rank
   size_t slot_stride;            // doubles between the two slots of a rank's buffer
   double* peer_q[kMaxPeers];     // [rank] -> that rank's buffer: 2 slots x slot_stride doubles
   unsigned int* peer_flag[kMaxPeers];  // [rank] -> that rank's 2 flags (one per slot, 128 bytes apart)
@@ -177,13 +180,15 @@ cg_step_kernel(const CgStepArgs a) {
     }
     if (a.world > 1 && a.q == nullptr) {
       // ---- all-reduce of q over the ranks through peer memory ----
-      const int slot = a.epoch & 1u;
+      const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(a.epoch) + 1u;  // (read before barrier 1)
+      const int slot = epoch & 1u;
       if (on) a.peer_q[a.rank][slot * a.slot_stride + o9] = q;
-      GridBarrier(st, gen);  // every CTA of this rank has published
+      GridBarrier(st, gen);  // every CTA of this rank has published (and has read the epoch counter)
       if (threadIdx.x == 0) {
         if (blockIdx.x == 0) {
+          *a.epoch = epoch;
           __threadfence_system();
-          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(a.epoch) : "memory");
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(epoch) : "memory");
         }
         for (int rk = 0; rk < a.world; ++rk) {
           if (rk == a.rank) continue;
@@ -194,7 +199,7 @@ cg_step_kernel(const CgStepArgs a) {
             asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[rk] + slot * 32) : "memory");
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
             if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }  // never hang the GPU
-          } while (seen != a.epoch);
+          } while (seen != epoch);
         }
       }
       __syncthreads();
@@ -225,6 +230,7 @@ cg_step_kernel(const CgStepArgs a) {
       if (writer) Finish(st, CB200_LINEAR_SOLVER_FAILURE, kReasonAlphaFailure);
       return;
     }
+    if (writer && it <= kHistCap) st->alpha_hist[it - 1] = alpha;  // x += alpha p follows (stream_kernels.cuh: history)
     // ---- x += alpha p (:216) ----
     if (on) {
       x += alpha * p;
@@ -304,44 +310,43 @@ cg_step_kernel(const CgStepArgs a) {
 namespace cb200 {
 
 // ----------------------------------------------------------------------------
-// The same exchange for the per-solve sums (reduced rhs, preconditioner blocks):
-// buf[0..n) <- sum over ranks, in rank order, through the peer-mapped buffers.
-// Two plain launches: peer_publish_kernel copies the local partial into this rank's
-// slot and its last CTA releases the epoch flag; peer_sum_kernel waits for every
-// peer's flag and adds the slots up. The kernel boundary orders publish before sum
-// on this GPU; the flags order it across GPUs. Any CTA of the sum kernel can make
-// progress on its own, so no cooperative launch is needed.
+// The same exchange for the per-solve sums (reduced rhs, preconditioner blocks, the
+// scalars of the trust-region loop): buf[0..n) <- sum (or max) over ranks, in rank
+// order, through the peer-mapped buffers. ONE plain launch of <= 64 CTAs: every CTA
+// copies its part of the local partial into this rank's slot; the last one to do so
+// releases the epoch flag; every CTA then waits for all peers' flags and adds the
+// slots up. A waiting CTA only needs CTAs of OTHER GPUs (and its own grid's, all of
+// which fit the device at once) to make progress, so no cooperative launch is needed.
+// The exchange number lives on the device (CgState::peer_epoch[channel]) and is
+// advanced by the last CTA to finish, i.e. after every CTA has read it.
 // ----------------------------------------------------------------------------
 struct PeerRefs {
   int world, rank;
-  unsigned int epoch;
+  int channel;                   // 0: main stream, 1: side stream (own buffers, flags, counter, tickets)
   size_t slot_stride;
+  unsigned int* epoch;           // &CgState::peer_epoch[channel]
   double* base[kMaxPeers];
   unsigned int* flag[kMaxPeers];
 };
 
+template <bool MAX>
 __global__ void __launch_bounds__(256)
-peer_publish_kernel(const PeerRefs p, const double* __restrict__ buf, size_t n, CgState* st) {
-  const int slot = p.epoch & 1u;
+peer_allreduce_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgState* st) {
+  const unsigned int epoch = *reinterpret_cast<volatile unsigned int*>(p.epoch) + 1u;
+  const int slot = epoch & 1u;
   double* mine = p.base[p.rank] + slot * p.slot_stride;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     mine[i] = buf[i];
   __threadfence();
   __syncthreads();
   if (threadIdx.x == 0) {
-    const unsigned int t = atomicAdd(&st->ticket[4], 1u);
+    unsigned int* ticket = &st->ticket[4 + 2 * p.channel];
+    const unsigned int t = atomicAdd(ticket, 1u);
     if (t == gridDim.x - 1) {
-      st->ticket[4] = 0;
+      *ticket = 0;
       __threadfence_system();
-      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flag[p.rank] + slot * 32), "r"(p.epoch) : "memory");
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flag[p.rank] + slot * 32), "r"(epoch) : "memory");
     }
-  }
-}
-
-__global__ void __launch_bounds__(256)
-peer_sum_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgState* st) {
-  const int slot = p.epoch & 1u;
-  if (threadIdx.x == 0) {
     for (int r = 0; r < p.world; ++r) {
       if (r == p.rank) continue;
       unsigned int seen;
@@ -351,14 +356,31 @@ peer_sum_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgState* s
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[r] + slot * 32) : "memory");
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
         if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }
-      } while (seen != p.epoch);
+      } while (seen != epoch);
+    }
+    // (own flag: the sum below also reads this rank's slot, complete only when every CTA has published)
+    if (gridDim.x > 1) {
+      unsigned int seen;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[p.rank] + slot * 32) : "memory");
+      } while (seen != epoch && !*reinterpret_cast<volatile int*>(&st->peer_timeout));
     }
   }
   __syncthreads();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    double s = 0.0;
-    for (int r = 0; r < p.world; ++r) s += __ldcg(p.base[r] + slot * p.slot_stride + i);  // rank order
+    double s = __ldcg(p.base[0] + slot * p.slot_stride + i);
+    for (int r = 1; r < p.world; ++r) {  // rank order: bit-identical on every rank
+      const double v = __ldcg(p.base[r] + slot * p.slot_stride + i);
+      s = MAX ? fmax(s, v) : s + v;
+    }
     buf[i] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int* ticket = &st->ticket[5 + 2 * p.channel];
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    if (t == gridDim.x - 1) { *ticket = 0; *p.epoch = epoch; }
   }
 }
 

@@ -4,7 +4,14 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <map>
+#include <mutex>
+#include <set>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "cg_kernels.cuh"
@@ -25,6 +32,66 @@ struct Nccl {
   int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
+};
+
+// One of the two sets of peer-mapped partial-sum buffers of a multi-GPU solver (cg_step.cuh): channel 0
+// belongs to the main stream's sequence of sums, channel 1 to the side stream's (the reduced rhs of a
+// forked solve start). Layout of a rank's buffer: 2 slots x `slot` doubles, then 2 flags 128 bytes apart.
+struct PeerChannel {
+  void* d_buf = nullptr;      // this rank's buffer
+  size_t slot = 0;            // doubles per slot
+  void* base[16] = {};        // every rank's buffer as addressable from this device (own = d_buf)
+  bool ipc = false;           // peers' buffers came from cudaIpcOpenMemHandle (one process per GPU)
+};
+
+// Host rendezvous of the shard contexts of ONE multi-GPU handle (cb200_options::num_gpus > 1): the
+// shards live in one process, so buffer addresses and small agreement values travel through host memory.
+struct InProcGroup {
+  int world = 0;
+  std::mutex m;
+  std::condition_variable cv;
+  int arrived = 0;
+  unsigned generation = 0;
+  void* peer_buf[2][16] = {};
+  double value[16] = {};
+  char nccl_id[128] = {};
+  bool aborted = false;       // a shard failed during construction: nobody waits for it any more
+  bool Barrier() {
+    std::unique_lock<std::mutex> lock(m);
+    const unsigned gen = generation;
+    if (++arrived == world) { arrived = 0; ++generation; cv.notify_all(); }
+    else cv.wait(lock, [&] { return generation != gen || aborted; });
+    return !aborted;
+  }
+  void Abort() {
+    std::lock_guard<std::mutex> lock(m);
+    aborted = true;
+    cv.notify_all();
+  }
+  double Sum(int rank, double v) {  // every shard calls it; all get the same sum (rank order); -1 after Abort
+    value[rank] = v;
+    if (!Barrier()) return -1.0;
+    double s = 0.0;
+    for (int r = 0; r < world; ++r) s += value[r];
+    if (!Barrier()) return -1.0;
+    return s;
+  }
+};
+
+// The worker threads of a multi-GPU handle: one per shard, each bound to its device. A call on the
+// handle posts one task, every worker runs it on its shard, the caller waits for all of them.
+struct MultiGpu {
+  std::vector<cb200_solver*> shards;
+  InProcGroup group;
+  std::vector<std::thread> threads;
+  std::mutex m;
+  std::condition_variable cv_work, cv_done;
+  std::atomic<unsigned> posted{0};   // tasks posted so far (workers spin on it briefly before sleeping)
+  std::function<int(cb200_solver*, int)> task;
+  int pending = 0;
+  bool stop = false;
+  std::vector<int> rc;
+  std::vector<std::string> error;
 };
 
 }  // namespace cb200
@@ -102,14 +169,33 @@ struct cb200_solver {
   bool ex_ready = false;                // d_S holds the matrix of the resident values / D
 
   cb200::Nccl nccl;
-  // fused all-reduce of the PCG step over NVLink peer memory (cg_step.cuh); null = NCCL path
-  void* d_peer_buf = nullptr;                 // this rank's 2 slots x peer_slot doubles + 2 flags
-  size_t peer_slot = 0;                       // doubles per slot (81 C: the largest per-solve sum)
+  // sums over the GPUs through NVLink peer memory (cg_step.cuh); peer_allreduce false = NCCL path
+  cb200::PeerChannel peer[2];
   long long global_dup_pairs = 0;             // duplicate (point, camera) pairs over all ranks
-  void* peer_base[16] = {};                   // every rank's buffer as mapped here (own = d_peer_buf)
-  unsigned int peer_epoch = 0;
   bool peer_allreduce = false;
-  int stream_ctas_per_sm[4][2] = {};          // occupancy of point_stream_kernel<MODE, BUILD>, filled on first use
+  // multi-GPU handle (cb200_options::num_gpus > 1): `multi` on the handle the caller holds, `group` on its shards
+  cb200::MultiGpu* multi = nullptr;
+  cb200::InProcGroup* group = nullptr;
+  bool writes_replicated = true;              // this shard writes camera-sized (replicated) results to host memory
+  // back substitution from the per-iteration history (stream_kernels.cuh, StreamArgs::v_store)
+  double *d_v_rhs = nullptr, *d_v_hist = nullptr;
+  bool use_history = false;
+  // deterministic mode: per-chunk partial sums of the camera gather
+  double* d_chunk_partial9 = nullptr;
+  // chunked upload of cb200_solve: tile / row ranges of the chunks, copy stream, one event per chunk
+  std::vector<int> chunk_tile, chunk_row;     // h2d_chunks + 1 entries each
+  cudaStream_t copy_stream = nullptr;
+  std::vector<cudaEvent_t> chunk_event;
+  cudaEvent_t ev_copy_start = nullptr;
+  // CUDA graphs of the launch sequences of a solve, by sequence key; any change of a launch parameter
+  // (diagonal on / off, trace, model pointer ...) bumps graph_config and drops them
+  bool graphs_ok = false;
+  long long graph_sig = 0;
+  std::map<long long, cudaGraphExec_t> graphs;
+  std::map<long long, int> graph_launches;    // kernels inside each graph
+  std::set<long long> graph_seen;             // sequences that already ran once un-captured (warm-up)
+  cb200::CgState* h_cg_init = nullptr;        // pinned: the head a solve starts from (source of the graph's H2D node)
+  int stream_ctas_per_sm[4][4] = {};          // occupancy of point_stream_kernel<MODE, BUILD, DET>, filled on first use
   int launches = 0;
   std::vector<void*> allocations;
 };

@@ -26,6 +26,7 @@
 #ifndef CB200_STREAM_KERNELS_CUH_
 #define CB200_STREAM_KERNELS_CUH_
 
+#include "cg_kernels.cuh"
 #include "kernels.cuh"
 
 namespace cb200 {
@@ -60,6 +61,19 @@ struct StreamArgs {
   int run_when_done;        // ... or, if this is non-zero, when it is NOT set (speculative back substitution)
   double* model;            // (kModeBack) or null: accumulates sum_rows m.(b - m/2) with m = E y_e + F x, the
                             // model cost change of the step -y (trust_region_minimizer.cc:430-438)
+  // Back substitution without a pass over the Jacobian: y_e = (E'E+D^2)^-1 E'(b - F x) with x = sum_k alpha_k p_k
+  // equals v_rhs - sum_k alpha_k v_k, v_k being exactly the per-point intermediate of the k-th S*p pass. The rhs
+  // pass stores v_rhs, the first kHistCap S*p passes store their v (24 bytes per point each), and a solve that
+  // ends within kHistCap iterations combines them (point_combine_kernel) instead of streaming J once more.
+  double* v_store;          // (kModeRhs) [3P] or null: v of every point
+  double* v_hist;           // (kModeSx) [kHistCap x v_hist_stride] or null: v of every point of PCG iteration cg->iter
+  size_t v_hist_stride;
+  const CgState* cg;        // with v_hist, or (kModeBack) to skip the pass when the history covers the solve
+  double* rows_out;         // (DET) [2N]: w_r of every row instead of the atomic scatter of F_r' w_r
+  unsigned long long* stamp;  // or null: CTA 0 writes %globaltimer here at entry (start of a solve)
+  int zero_points;          // (kModeBack) y_e = 0 instead of the back-substituted value: the step [0; x] of an explicit
+                            // Schur solve that ended without SUCCESS (schur_complement_solver.cc:135-160), whose model
+                            // cost change the trust-region loop still needs (trust_region_minimizer.cc:430-447)
 };
 
 template <int MODE, bool BUILD>
@@ -124,12 +138,20 @@ __device__ __forceinline__ double SegScan(double v, const SegMask& k) {
   return v;
 }
 
-template <int MODE, bool BUILD>
+template <int MODE, bool BUILD, bool DET = false>
 __global__ void __launch_bounds__(kStreamThreads, 3)
 point_stream_kernel(const StreamArgs a) {
   using L = StreamLayout<MODE, BUILD>;
   static_assert(!BUILD || MODE == kModeRhs, "the E'E build rides on the rhs pass");
   if (a.done != nullptr && ((*a.done != 0) != (a.run_when_done != 0))) return;
+  if (MODE == kModeBack && a.cg != nullptr && a.cg->hist_valid && a.cg->iter <= kHistCap) return;  // point_combine_kernel does it
+  if (a.stamp != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *a.stamp = GlobalTimerNs();
+  // (kModeSx) slot of this product's v in the history, or -1
+  int hist_slot = -1;
+  if (MODE == kModeSx && a.v_hist != nullptr) {
+    const int it = a.cg->iter;
+    if (a.cg->hist_valid && it >= 1 && it <= kHistCap) hist_slot = it - 1;
+  }
   extern __shared__ __align__(128) unsigned char smem[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
@@ -326,8 +348,17 @@ point_stream_kernel(const StreamArgs a) {
       v0 = inv[0] * u0 + inv[1] * u1 + inv[2] * u2;
       v1 = inv[1] * u0 + inv[3] * u1 + inv[4] * u2;
       v2 = inv[2] * u0 + inv[4] * u1 + inv[5] * u2;
+      if (MODE == kModeBack && a.zero_points) { v0 = 0.0; v1 = 0.0; v2 = 0.0; }
       if (MODE == kModeBack) {
         double* y = a.y_e + (size_t)(p0 + pt) * 3;
+        y[0] = v0; y[1] = v1; y[2] = v2;
+      }
+      if (MODE == kModeRhs && a.v_store != nullptr) {
+        double* y = a.v_store + (size_t)(p0 + pt) * 3;
+        y[0] = v0; y[1] = v1; y[2] = v2;
+      }
+      if (MODE == kModeSx && hist_slot >= 0) {
+        double* y = a.v_hist + (size_t)hist_slot * a.v_hist_stride + (size_t)(p0 + pt) * 3;
         y[0] = v0; y[1] = v1; y[2] = v2;
       }
     }
@@ -369,8 +400,14 @@ point_stream_kernel(const StreamArgs a) {
       const double ev1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
       const double w0 = (MODE == kModePseZ) ? ev0 : t0 - ev0;
       const double w1 = (MODE == kModePseZ) ? ev1 : t1 - ev1;
+      if (DET) {
+        // deterministic mode: the row's w leaves as is; camera_gather_kernel sums F_r' w_r per camera in a fixed order
+        if (active && !(BUILD && a.b == nullptr))
+          reinterpret_cast<double2*>(a.rows_out)[(size_t)r0 + lane] = make_double2(w0, w1);
+      } else {
 #pragma unroll
-      for (int k = 0; k < 9; ++k) sXw[lane * 9 + k] = Fi[k] * w0 + Fi[9 + k] * w1;
+        for (int k = 0; k < 9; ++k) sXw[lane * 9 + k] = Fi[k] * w0 + Fi[9 + k] * w1;
+      }
     }
     if (BUILD && a.weights != nullptr) {
       // W_r = I - E_r c E_r' with c the adjugate inverse (InvertPSDMatrix<3>)
@@ -388,7 +425,7 @@ point_stream_kernel(const StreamArgs a) {
       }
     }
     __syncwarp();
-    if (!(BUILD && a.b == nullptr)) {
+    if (!DET && !(BUILD && a.b == nullptr)) {
 #pragma unroll
       for (int j = 0; j < 9; ++j) {
         const int idx = j * 32 + lane;
@@ -433,6 +470,7 @@ __global__ void __launch_bounds__(256)
 point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
                   const int* __restrict__ row_start, const int* __restrict__ cam) {
   if (a.done != nullptr && ((*a.done != 0) != (a.run_when_done != 0))) return;
+  if (MODE == kModeBack && a.cg != nullptr && a.cg->hist_valid && a.cg->iter <= kHistCap) return;
   __shared__ double sbuf[8];
   const int p = long_points[blockIdx.x];
   const int r0 = row_start[p], r1 = row_start[p + 1];
@@ -477,9 +515,19 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
   } else {
     for (int k = 0; k < 6; ++k) inv[k] = a.ete_inv[(size_t)p * 6 + k];
   }
-  const double v0 = inv[0] * u[0] + inv[1] * u[1] + inv[2] * u[2];
-  const double v1 = inv[1] * u[0] + inv[3] * u[1] + inv[4] * u[2];
-  const double v2 = inv[2] * u[0] + inv[4] * u[1] + inv[5] * u[2];
+  const bool zero = MODE == kModeBack && a.zero_points;
+  const double v0 = zero ? 0.0 : inv[0] * u[0] + inv[1] * u[1] + inv[2] * u[2];
+  const double v1 = zero ? 0.0 : inv[1] * u[0] + inv[3] * u[1] + inv[4] * u[2];
+  const double v2 = zero ? 0.0 : inv[2] * u[0] + inv[4] * u[1] + inv[5] * u[2];
+  if (threadIdx.x == 0) {
+    double* vs = nullptr;
+    if (MODE == kModeRhs) vs = a.v_store;
+    if (MODE == kModeSx && a.v_hist != nullptr) {
+      const int it = a.cg->iter;
+      if (a.cg->hist_valid && it >= 1 && it <= kHistCap) vs = a.v_hist + (size_t)(it - 1) * a.v_hist_stride;
+    }
+    if (vs != nullptr) { vs[3 * (size_t)p] = v0; vs[3 * (size_t)p + 1] = v1; vs[3 * (size_t)p + 2] = v2; }
+  }
   if (MODE == kModeBack) {
     if (threadIdx.x == 0) { a.y_e[3 * (size_t)p] = v0; a.y_e[3 * (size_t)p + 1] = v1; a.y_e[3 * (size_t)p + 2] = v2; }
     if (a.model != nullptr) {
@@ -523,8 +571,32 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
     const double ev1 = Ei[3] * v0 + Ei[4] * v1 + Ei[5] * v2;
     const double w0 = (MODE == kModePseZ) ? ev0 : t0 - ev0;
     const double w1 = (MODE == kModePseZ) ? ev1 : t1 - ev1;
+    if (a.rows_out != nullptr) {  // deterministic mode
+      a.rows_out[2 * (size_t)r] = w0; a.rows_out[2 * (size_t)r + 1] = w1;
+      continue;
+    }
     double* yc = y + 10 * (size_t)cam[r];
     for (int k = 0; k < 9; ++k) atomicAdd(yc + k, Fi[k] * w0 + Fi[9 + k] * w1);
+  }
+}
+
+// Back substitution from the history (see StreamArgs::v_store): y_e = v_rhs - sum_{k < iter} alpha_k v_k.
+// Runs behind a finished solve (done set) that stayed within kHistCap iterations; otherwise the
+// kModeBack pass does the work. One thread per entry of y_e; fixed order => deterministic.
+__global__ void __launch_bounds__(256)
+point_combine_kernel(const CgState* __restrict__ st, const double* __restrict__ v_rhs,
+                     const double* __restrict__ v_hist, size_t stride, size_t n, double* __restrict__ y_e) {
+  if (!st->done || !st->hist_valid || st->iter > kHistCap) return;
+  const int iters = st->iter;
+  double alpha[kHistCap];
+#pragma unroll
+  for (int k = 0; k < kHistCap; ++k) alpha[k] = st->alpha_hist[k];
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    double y = v_rhs[i];
+#pragma unroll
+    for (int k = 0; k < kHistCap; ++k)
+      if (k < iters && alpha[k] != 0.0) y -= alpha[k] * v_hist[(size_t)k * stride + i];
+    y_e[i] = y;
   }
 }
 

@@ -34,7 +34,9 @@ class COptions(ctypes.Structure):
                 ("device_id", ctypes.c_int), ("rank", ctypes.c_int), ("world_size", ctypes.c_int),
                 ("nccl_unique_id", ctypes.c_char_p), ("y_replicas", ctypes.c_int),
                 ("status_check_period", ctypes.c_int), ("use_explicit_schur_complement", ctypes.c_int),
-                ("explicit_switch_iterations", ctypes.c_int)]
+                ("explicit_switch_iterations", ctypes.c_int), ("num_gpus", ctypes.c_int),
+                ("device_ids", ctypes.c_int * 16), ("deterministic", ctypes.c_int),
+                ("cuda_graphs", ctypes.c_int), ("h2d_chunks", ctypes.c_int)]
 
 
 class CSummary(ctypes.Structure):
@@ -42,7 +44,7 @@ class CSummary(ctypes.Structure):
                 ("termination_type", ctypes.c_int), ("message", ctypes.c_char * 512),
                 ("h2d_ms", ctypes.c_float), ("setup_ms", ctypes.c_float), ("pcg_ms", ctypes.c_float),
                 ("back_substitute_ms", ctypes.c_float), ("d2h_ms", ctypes.c_float),
-                ("kernel_launches", ctypes.c_int)]
+                ("kernel_launches", ctypes.c_int), ("total_ms", ctypes.c_float)]
 
 
 class CLmOptions(ctypes.Structure):
@@ -251,7 +253,8 @@ class IterativeSchurComplementSolver:
                  max_num_iterations=500, residual_reset_period=10, use_spse_initialization=False,
                  max_num_spse_iterations=5, spse_tolerance=0.1, device_id=0, rank=0, world_size=1,
                  nccl_unique_id=None, y_replicas=0, status_check_period=0,
-                 use_explicit_schur_complement=False, explicit_switch_iterations=0):
+                 use_explicit_schur_complement=False, explicit_switch_iterations=0, num_gpus=0, device_ids=None,
+                 deterministic=False, cuda_graphs=0, h2d_chunks=0):
         self.L = lib()
         self.structure = structure
         cs = structure.c_struct()
@@ -259,7 +262,8 @@ class IterativeSchurComplementSolver:
                        max_num_iterations, residual_reset_period, int(use_spse_initialization),
                        max_num_spse_iterations, spse_tolerance, device_id, rank, world_size,
                        nccl_unique_id, y_replicas, status_check_period, int(use_explicit_schur_complement),
-                       explicit_switch_iterations)
+                       explicit_switch_iterations, num_gpus, (ctypes.c_int * 16)(*(device_ids or [])),
+                       int(deterministic), cuda_graphs, h2d_chunks)
         h = _H()
         _check(self.L.cb200_create(ctypes.byref(cs), ctypes.byref(opt), ctypes.byref(h)))
         self.h = h
@@ -284,7 +288,7 @@ class IterativeSchurComplementSolver:
         return {"num_iterations": s.num_iterations, "termination_type": s.termination_type,
                 "message": s.message.decode(), "h2d_ms": s.h2d_ms, "setup_ms": s.setup_ms,
                 "pcg_ms": s.pcg_ms, "back_substitute_ms": s.back_substitute_ms, "d2h_ms": s.d2h_ms,
-                "kernel_launches": s.kernel_launches}
+                "kernel_launches": s.kernel_launches, "total_ms": s.total_ms}
 
     # --- LinearSolver::Solve ---------------------------------------------------------------
     def solve(self, values, b, D, q_tolerance=0.0, r_tolerance=0.0, x=None):

@@ -69,20 +69,38 @@ FlatBlockStructure FlattenBlockStructure(const Bs& bs) {
 
 #ifdef CERES_INTERNAL_LINEAR_SOLVER_H_  // only inside a Ceres tree, after "ceres/linear_solver.h"
 
+#include <cstdlib>
+#include <memory>
+
+#include "absl/log/check.h"  // as linear_solver.h:43 (this tree logs through abseil, not glog)
 #include "ceres/block_sparse_matrix.h"
 #include "ceres/block_structure.h"
-#include "glog/logging.h"
 
 namespace ceres::internal {
 
 class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver {
  public:
-  explicit B200IterativeSchurComplementSolver(LinearSolver::Options options)
-      : options_(std::move(options)) {}
+  // `fallback`: the solver LinearSolver::Create returned for this configuration before the patch
+  // (IterativeSchurComplementSolver, or SparseSchurComplementSolver with use_explicit_schur_complement;
+  // linear_solver.cc:111-116). Problems OUTSIDE the device path's scope -- block structures that are not
+  // <2,3,9> bundle adjustment (camera priors or other F-only rows, other block sizes, no F blocks at all:
+  // iterative_schur_complement_solver.cc:85-93), CLUSTER_* preconditioners -- are handed to it unchanged, so
+  // the patch never turns a Solve() that used to work into a failure. Device errors are never delegated:
+  // they are FATAL_ERROR. Without a fallback, out-of-scope problems are FATAL_ERROR too.
+  explicit B200IterativeSchurComplementSolver(LinearSolver::Options options,
+                                              std::unique_ptr<LinearSolver> fallback = nullptr)
+      : options_(std::move(options)), fallback_(std::move(fallback)) {}
   ~B200IterativeSchurComplementSolver() override {
     if (registered_values_ != nullptr) cb200_host_unregister(registered_values_);
     cb200_destroy(handle_);
   }
+
+  // GPUs one handle drives (cb200_options::num_gpus / device_ids): LinearSolver::Options has no field for
+  // device placement, so it comes from the environment of the process that calls ceres::Solve:
+  //   CERES_B200_NUM_GPUS=4            GPUs 0..3
+  //   CERES_B200_DEVICES=2,3,6,7       these CUDA ordinals (implies their count)
+  //   CERES_B200_DETERMINISTIC=1       bitwise-repeatable solves (fixed-order camera sums)
+  int num_gpus() const { return num_gpus_; }
 
  private:
   static int PreconditionerCode(PreconditionerType t) {
@@ -91,8 +109,26 @@ class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver 
       case JACOBI: return CB200_JACOBI;
       case SCHUR_JACOBI: return CB200_SCHUR_JACOBI;
       case SCHUR_POWER_SERIES_EXPANSION: return CB200_SCHUR_POWER_SERIES_EXPANSION;
-      default: return -1;  // CLUSTER_*: rejected by cb200_create, no CPU fallback
+      default: return -1;  // CLUSTER_*: outside the device path
     }
+  }
+
+  static void PlacementFromEnvironment(cb200_options* o) {
+    if (const char* e = std::getenv("CERES_B200_DEVICES")) {
+      int n = 0;
+      for (const char* p = e; *p != '\0' && n < 16;) {
+        char* end = nullptr;
+        const long v = std::strtol(p, &end, 10);
+        if (end == p) break;
+        o->device_ids[n++] = static_cast<int>(v);
+        p = (*end == ',') ? end + 1 : end;
+      }
+      o->num_gpus = n;
+      if (n == 1) { o->device_id = o->device_ids[0]; o->num_gpus = 0; }
+    } else if (const char* e = std::getenv("CERES_B200_NUM_GPUS")) {
+      o->num_gpus = std::atoi(e);
+    }
+    if (const char* e = std::getenv("CERES_B200_DETERMINISTIC")) o->deterministic = std::atoi(e) != 0;
   }
 
   LinearSolver::Summary SolveImpl(BlockSparseMatrix* A, const double* b,
@@ -100,7 +136,8 @@ class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver 
                                   double* x) final {
     CHECK(A->block_structure() != nullptr);
     LinearSolver::Summary summary;
-    if (handle_ == nullptr) {  // same sparsity structure for every later call
+    if (delegate_) return fallback_->Solve(A, b, per_solve_options, x);
+    if (handle_ == nullptr) {  // same sparsity structure for every later call (linear_solver.h:137-142)
       const ceres_b200::FlatBlockStructure flat = ceres_b200::FlattenBlockStructure(*A->block_structure());
       const cb200_structure view = flat.view();
       cb200_options o{};
@@ -118,15 +155,24 @@ class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver 
       o.device_id = 0;
       o.rank = 0;
       o.world_size = 1;
-      if (cb200_create(&view, &o, &handle_) != CB200_OK) {
+      PlacementFromEnvironment(&o);
+      const int rc = cb200_create(&view, &o, &handle_);
+      if ((rc == CB200_ERR_UNSUPPORTED_STRUCTURE || rc == CB200_ERR_INVALID_ARGUMENT) && fallback_ != nullptr) {
+        delegate_ = true;  // out of the device path's scope: the reference's own solver, as before the patch
+        return fallback_->Solve(A, b, per_solve_options, x);
+      }
+      if (rc != CB200_OK) {
         summary.termination_type = LinearSolverTerminationType::FATAL_ERROR;
         summary.message = cb200_last_error();
         return summary;
       }
+      num_gpus_ = o.num_gpus > 1 ? o.num_gpus : 1;
     }
     if (registered_values_ != A->values()) {
       // the Jacobian's value array keeps its address for the whole Solve(): page-lock it once, so that the
-      // 24 N doubles cross PCIe at full rate every iteration (best effort: the solve works without it)
+      // 24 N doubles cross PCIe at full rate every iteration (best effort: the solve works without it; the
+      // one-off cost is that of cudaHostRegister). A BlockSparseMatrix created with
+      // use_page_locked_memory (block_sparse_matrix.cc:178-180) is already pinned: registering is then a no-op.
       if (registered_values_ != nullptr) cb200_host_unregister(registered_values_);
       registered_values_ = nullptr;
       if (cb200_host_register(A->values(), sizeof(double) * static_cast<size_t>(A->num_nonzeros())) == CB200_OK)
@@ -147,8 +193,11 @@ class B200IterativeSchurComplementSolver final : public BlockSparseMatrixSolver 
   }
 
   LinearSolver::Options options_;
+  std::unique_ptr<LinearSolver> fallback_;
+  bool delegate_ = false;
   cb200_solver* handle_ = nullptr;
   const double* registered_values_ = nullptr;
+  int num_gpus_ = 1;
 };
 
 }  // namespace ceres::internal

@@ -76,10 +76,15 @@ typedef struct cb200_options {
   int use_spse_initialization;
   int max_num_spse_iterations;
   double spse_tolerance;
-  /* device placement: one process per GPU. rank/world_size shard the points
-   * (and their residual rows) into contiguous ranges of balanced observation
-   * count; world_size > 1 needs nccl_unique_id (128 bytes from
-   * cb200_nccl_unique_id on rank 0, broadcast by the caller). */
+  /* device placement, two ways (linear_solver.h:150-230 has num_threads / context for the same job):
+   * (a) ONE handle drives several GPUs of the box from the caller's thread (what a single-process
+   *     ceres::Solve needs): leave rank = 0, world_size = 1 and set num_gpus (and optionally
+   *     device_ids; default 0 .. num_gpus-1). The library shards the points over the GPUs, runs one
+   *     internal worker thread per GPU and sums the camera-sized partials through NVLink peer
+   *     memory (cudaDeviceEnablePeerAccess; no NCCL on the implicit path).
+   * (b) one process per GPU: rank/world_size shard the points (and their residual rows) into
+   *     contiguous ranges of balanced observation count; world_size > 1 needs nccl_unique_id
+   *     (128 bytes from cb200_nccl_unique_id on rank 0, broadcast by the caller). num_gpus <= 1. */
   int device_id;
   int rank;
   int world_size;
@@ -102,6 +107,18 @@ typedef struct cb200_options {
                                  operator, same preconditioner, same vectors; products
                                  agree to 1e-12). Not a reference option: an internal
                                  speed-up for long solves.              */
+  int num_gpus;               /* 0 / 1 = one GPU (device_id). n > 1 = mode (a) above      */
+  int device_ids[16];         /* mode (a): CUDA ordinals; all zero = 0 .. num_gpus-1      */
+  int deterministic;          /* 1 = bitwise-repeatable solves: the camera scatter F'w of every
+                                 product is summed per camera in a fixed order (a second,
+                                 camera-major pass) instead of FP64 atomics, so borderline
+                                 convergence tests cannot flip between runs. About 2x the time
+                                 per product. Implicit operator only.                        */
+  int cuda_graphs;            /* 0 = default (on): the launch sequence of a solve is captured once
+                                 and replayed as CUDA graphs; -1 = off (plain stream launches)  */
+  int h2d_chunks;             /* 0 = default (16): cb200_solve copies the Jacobian in this many
+                                 point-range chunks and runs the E'E / rhs pass on each chunk
+                                 while the next one is still crossing PCIe; 1 = one copy      */
 } cb200_options;
 
 /* LinearSolver::Summary (linear_solver.h:320-326) + per-phase device timings. */
@@ -110,9 +127,13 @@ typedef struct cb200_summary {
   int num_iterations;
   int termination_type;
   char message[512];
-  /* milliseconds, CUDA events on the solver's stream */
+  /* milliseconds: h2d / d2h / total from CUDA events on the solver's stream, the phases in between
+   * from %globaltimer stamps the kernels write at the phase boundaries */
   float h2d_ms, setup_ms, pcg_ms, back_substitute_ms, d2h_ms;
   int kernel_launches;        /* kernels launched by the last solve              */
+  float total_ms;             /* whole call on the device: cb200_solve_resident = setup + PCG + back
+                                 substitution; cb200_solve = first H2D byte to last D2H byte (with the
+                                 overlapped upload the phases above overlap, so they need not add up) */
 } cb200_summary;
 
 typedef struct cb200_solver cb200_solver;

@@ -8,12 +8,18 @@
 #include "../../include/ceres_b200_adapter.h"
 #include "../../ceres-solver-ceres-solver_b200/csrc/flatten.h"
 
+#ifdef CB200_REAL_BLOCK_STRUCTURE
+// the reference's own internal/ceres/block_structure.h (Eigen-free; export.h stubbed), where the tree is present
+#include "ceres/block_structure.h"
+namespace standin = ceres::internal;
+#else
 namespace standin {
 struct Block { int size = -1; int position = -1; };
 struct Cell { int block_id = -1; int position = -1; };
 struct CompressedList { Block block; std::vector<Cell> cells; int nnz = -1; int cumulative_nnz = -1; };
 struct CompressedRowBlockStructure { std::vector<Block> cols; std::vector<CompressedList> rows; };
 }  // namespace standin
+#endif
 
 int main(int argc, char** argv) {
   const int P = 40, C = 7;

@@ -1,4 +1,4 @@
-// Stand-in for glog (test only): CHECK aborts with a message.
+// Stand-in for abseil's absl/log/check.h (test only): CHECK aborts with a message.
 #pragma once
 #include <cstdio>
 #include <cstdlib>

@@ -9,6 +9,8 @@ import re
 import numpy as np
 import pytest
 
+REFERENCE_BLOCK_STRUCTURE = "/root/reference/internal/ceres/block_structure.h"
+
 from tests import util
 from tests.golden import kat_problems as kp
 
@@ -92,7 +94,14 @@ def test_adapter_header_flattens_a_ceres_block_structure(tmp_path):
     m = util.pkg()
     lib = m._build.build_cuda()
     exe = str(tmp_path / "adapter_driver")
-    subprocess.run(["g++", "-std=c++17", "-O1", "-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_driver.cc"),
+    real = []
+    if os.path.exists(REFERENCE_BLOCK_STRUCTURE):  # flatten the reference's own type where its header is present
+        inc = tmp_path / "real_headers" / "ceres"
+        inc.mkdir(parents=True, exist_ok=True)
+        (inc / "block_structure.h").write_text(f'#include "{REFERENCE_BLOCK_STRUCTURE}"\n')
+        real = ["-DCB200_REAL_BLOCK_STRUCTURE", "-I" + str(tmp_path / "real_headers"),
+                "-I" + os.path.join(util.ROOT, "tests", "cpp", "standin_ceres")]
+    subprocess.run(["g++", "-std=c++17", "-O1"] + real + ["-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_driver.cc"),
                     lib, "-Wl,-rpath," + os.path.dirname(lib)], check=True)
     out = subprocess.run([exe], check=True, capture_output=True, text=True).stdout
     kv = dict(t.split("=") for t in out.split())
@@ -137,12 +146,24 @@ def test_explicit_schur_option_validation():
 
 
 def build_adapter_class_driver(tmp_path):
+    """The adapter class against stand-ins for linear_solver.h / block_sparse_matrix.h / absl's check.h (the
+    include set of the v2.3.0 tree: abseil, no glog) and, where the reference tree is present (this
+    container, not the GPU box), against the reference's OWN internal/ceres/block_structure.h (Eigen-free;
+    only the generated export.h is stubbed) instead of the stand-in of the same name."""
     import subprocess
     m = util.pkg()
     lib = m._build.build_cuda()
     exe = str(tmp_path / "adapter_class_driver")
-    subprocess.run(["g++", "-std=c++17", "-O1", "-I" + os.path.join(util.ROOT, "tests", "cpp", "standin_ceres"),
-                    "-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_class_driver.cc"), lib,
+    standin = os.path.join(util.ROOT, "tests", "cpp", "standin_ceres")
+    includes = []
+    if os.path.exists(REFERENCE_BLOCK_STRUCTURE):
+        real = tmp_path / "real_headers" / "ceres"
+        real.mkdir(parents=True, exist_ok=True)
+        (real / "block_structure.h").write_text(f'#include "{REFERENCE_BLOCK_STRUCTURE}"\n')
+        includes.append("-I" + str(tmp_path / "real_headers"))
+    includes.append("-I" + standin)
+    subprocess.run(["g++", "-std=c++17", "-O1"] + includes +
+                   ["-o", exe, os.path.join(util.ROOT, "tests", "cpp", "adapter_class_driver.cc"), lib,
                     "-Wl,-rpath," + os.path.dirname(lib)], check=True)
     return exe
 
@@ -158,6 +179,33 @@ def test_adapter_class_compiles_and_reports_fatal_error_without_a_gpu(tmp_path):
     for mode in ("i", "e"):
         out = subprocess.run([exe, mode], check=True, capture_output=True, text=True).stdout
         assert "termination=3" in out and "no CUDA device" in out, out
+
+
+def test_adapter_class_delegates_out_of_scope_structures(tmp_path):
+    """A block structure outside the device path's scope (here a camera-prior row: one F cell, no E cell;
+    iterative_schur_complement_solver.cc handles it, DetectStructure falls back to dynamic sizes) goes to the
+    solver LinearSolver::Create returned before the patch, on the first call and on every later one; without
+    a fallback it is FATAL_ERROR with the library's reason. Decided before any device work: runs anywhere."""
+    import subprocess
+    exe = build_adapter_class_driver(tmp_path)
+    out = subprocess.run([exe, "u"], check=True, capture_output=True, text=True).stdout
+    assert "delegated_calls=2" in out and "x0=42" in out and "termination=0" in out, out
+    assert "delegated-to-reference-solver" in out, out
+    out = subprocess.run([exe, "U"], check=True, capture_output=True, text=True).stdout
+    assert "termination=3" in out and "cells" in out, out
+
+
+def test_no_schur_complement_blocks_is_unsupported():
+    """num_schur_complement_blocks == 0 (iterative_schur_complement_solver.cc:86-95; the shape of
+    LinearLeastSquaresProblem 3: E blocks only): outside the <2,3,9> scope -> CB200_ERR_UNSUPPORTED_STRUCTURE
+    from cb200_create before any device work (the adapter then delegates to the reference solver)."""
+    m = util.pkg()
+    P, N = 4, 8
+    rows = np.arange(N)
+    st = m.BlockStructure(np.full(N, 2), 2 * rows, np.arange(N + 1), rows // 2, 6 * rows, np.full(P, 3),
+                          3 * np.arange(P), P)
+    with pytest.raises(m.B200Error, match="cb200 error -2"):
+        m.IterativeSchurComplementSolver(st)
 
 
 def test_explicit_plan_invariants_host_only(tmp_path):

@@ -1,0 +1,152 @@
+"""ONE handle driving several GPUs (cb200_options::num_gpus, SURVEY 8(b) "Threading"): what a single-process
+ceres::Solve can reach through LinearSolver::Solve. Points sharded over the GPUs of the box, camera-sized
+sums through NVLink peer memory, one internal worker thread per GPU. Every result must match the un-sharded
+oracle within the same bars as one GPU. Skipped with fewer than 2 GPUs.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import binding as ob
+from tests import util
+from tests.test_gpu_parity import compare_solve
+
+pytestmark = pytest.mark.gpu
+
+OP_TOL = 1e-12
+ITERATE_TOL = 1e-9
+
+
+def gpu_counts():
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    return [k for k in (2, 3, 4, 8) if k <= n]
+
+
+def need_gpus():
+    if not gpu_counts():
+        pytest.skip("needs 2 GPUs")
+
+
+@pytest.mark.parametrize("ptype", ["SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION", "IDENTITY"])
+def test_multi_gpu_handle_matches_oracle(ptype):
+    need_gpus()
+    m = util.pkg()
+    p = m.SyntheticBAL.named("ladybug", scale=0.1, dup_pairs=5)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    st = p.structure
+    code = ["IDENTITY", "JACOBI", "SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION"].index(ptype)
+    o = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=code, max_num_iterations=300)
+    o.isc_init(values, D, residuals)
+    xv = np.random.default_rng(2).standard_normal(st.num_cols_f)
+    for n in gpu_counts():
+        # the whole solve, iterate by iterate, through the same helper as the one-GPU tests
+        compare_solve(m, st, values, residuals, D, ptype, q_tol=1e-3, r_tol=-1.0, max_it=300, threads=8, num_gpus=n)
+        g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, max_num_iterations=300, num_gpus=n)
+        assert (g.point_begin, g.point_end, g.row_begin, g.row_end) == (0, p.P, 0, p.N)
+        g.upload(values, residuals, D)
+        g.isc_init()
+        assert util.rel_err(g.isc_rhs(), o.isc_rhs()) < OP_TOL
+        assert util.rel_err(g.isc_multiply(xv), o.isc_multiply(xv)) < OP_TOL
+        assert util.rel_err(g.ete_inverse(), o.ete_inverse()) < OP_TOL
+        assert util.rel_err(g.isc_back_substitute(xv), o.isc_back_substitute(xv)) < OP_TOL
+        if ptype == "SCHUR_JACOBI":
+            assert util.rel_err(g.schur_jacobi(invert=False), o.schur_jacobi(values, D, invert=False)) < OP_TOL
+        # repeated solves through host buffers (graphs replayed, chunked upload) keep giving the same answer
+        x0, s0 = g.solve(values, residuals, D, 1e-3, -1.0)
+        for rep in range(3):
+            x, s = g.solve(values, residuals, D, 1e-3, -1.0)
+            assert s["num_iterations"] == s0["num_iterations"] and util.rel_err(x, x0) < 1e-11
+        g.close()
+
+
+def test_multi_gpu_handle_device_ids_and_errors():
+    need_gpus()
+    m = util.pkg()
+    p = m.SyntheticBAL(9, 200, 900, seed=3, geometry=False)
+    values, b, D = p.random_values(1)
+    D = np.abs(D) + 1.0
+    g = m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[1, 0])
+    x, s = g.solve(values, b, D, -1.0, 1e-10)
+    g.close()
+    g1 = m.IterativeSchurComplementSolver(p.structure)
+    x1, s1 = g1.solve(values, b, D, -1.0, 1e-10)
+    g1.close()
+    assert s["num_iterations"] == s1["num_iterations"] and util.rel_err(x, x1) < ITERATE_TOL
+    with pytest.raises(m.B200Error):
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[0, 0])
+    with pytest.raises(m.B200Error):
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[0, 99])
+    with pytest.raises(m.B200Error):
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, world_size=2, rank=0, nccl_unique_id=b"\0" * 128)
+
+
+def test_multi_gpu_handle_lm_loop_and_explicit():
+    need_gpus()
+    from oracle import lm_reference as lmr
+    m = util.pkg()
+    n = gpu_counts()[-1]
+    p = m.SyntheticBAL(31, 3000, 14000, seed=7, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+    st = p.structure
+    o = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=500)
+    want = lmr.minimize(p, p.cameras, p.points, lambda v, r, D, e: o.solve(v, r, D, e, -1.0), eta=1e-2,
+                        max_num_iterations=6)
+    g = m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=500, num_gpus=n)
+    g.bal_attach(p.observations)
+    g.bal_set_parameters(p.cameras, p.points)
+    got = g.lm_minimize(eta=1e-2, max_num_iterations=6)
+    cam, pts = g.bal_get_parameters()
+    g.close()
+    assert len(got["iterations"]) == len(want["iterations"])
+    for a, b in zip(got["iterations"], want["iterations"]):
+        assert a["linear_solver_iterations"] == b["linear_solver_iterations"], (a, b)
+        assert abs(a["cost"] - b["cost"]) <= 1e-8 * b["cost"], (a, b)
+    assert abs(got["final_cost"] - want["final_cost"]) <= 1e-8 * want["final_cost"]
+    assert util.rel_err(cam, want["cameras"]) < 1e-7 and util.rel_err(pts, want["points"]) < 1e-7
+    # use_explicit_schur_complement through the same kind of handle (cells summed over the GPUs by NCCL)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    xo, so = o.explicit_solve(values, residuals, D, 1e-3, -1.0)
+    ge = m.IterativeSchurComplementSolver(st, preconditioner_type=m.SCHUR_JACOBI, max_num_iterations=500,
+                                          num_gpus=n, use_explicit_schur_complement=True)
+    xe, se = ge.solve(values, residuals, D, 1e-3, -1.0)
+    ge.close()
+    assert se["num_iterations"] == so["num_iterations"] and util.rel_err(xe, xo) < ITERATE_TOL
+
+
+def test_multi_gpu_handle_deterministic():
+    need_gpus()
+    m = util.pkg()
+    n = gpu_counts()[0]
+    p = m.SyntheticBAL.named("ladybug", scale=0.1)
+    values, residuals, D, _, _ = util.lm_like_problem(p)
+    xs = []
+    for handle in range(2):
+        g = m.IterativeSchurComplementSolver(p.structure, max_num_iterations=300, num_gpus=n, deterministic=True)
+        for rep in range(2):
+            x, s = g.solve(values, residuals, D, 1e-3, -1.0)
+            xs.append(x.copy())
+        g.close()
+    for x in xs[1:]:
+        assert np.array_equal(x, xs[0])
+    compare_solve(m, p.structure, values, residuals, D, "SCHUR_JACOBI", q_tol=1e-3, r_tol=-1.0, max_it=300, threads=8,
+                  num_gpus=n, deterministic=True)
+
+
+def test_adapter_class_drives_two_gpus(tmp_path):
+    """The Ceres-side adapter (include/ceres_b200_adapter.h) through LinearSolver::Solve with
+    CERES_B200_NUM_GPUS=2: the same x as with one GPU to 1e-9 (VERDICT r1 'Next round' 3)."""
+    need_gpus()
+    import os
+    import subprocess
+    from tests.test_cpu_host import build_adapter_class_driver
+    exe = build_adapter_class_driver(tmp_path)
+    outs = []
+    for n in ("1", "2"):
+        env = dict(os.environ, CERES_B200_NUM_GPUS=n)
+        out = subprocess.run([exe, "i", str(tmp_path / f"x{n}.bin")], check=True, capture_output=True, text=True,
+                             timeout=120, env=env).stdout
+        kv = dict(t.split("=", 1) for t in out.split() if "=" in t)
+        assert kv["termination"] == "0", out
+        outs.append((kv, np.fromfile(tmp_path / f"x{n}.bin")))
+    assert outs[0][0]["iterations"] == outs[1][0]["iterations"]
+    assert outs[1][0]["gpus"] == "2"
+    assert util.rel_err(outs[1][1], outs[0][1]) < ITERATE_TOL
