@@ -39,8 +39,15 @@ def test_multi_gpu_handle_matches_oracle(ptype):
     o.isc_init(values, D, residuals)
     xv = np.random.default_rng(2).standard_normal(st.num_cols_f)
     for n in gpu_counts():
-        # the whole solve, iterate by iterate, through the same helper as the one-GPU tests
-        compare_solve(m, st, values, residuals, D, ptype, q_tol=1e-3, r_tol=-1.0, max_it=300, threads=8, num_gpus=n)
+        # the whole solve, iterate by iterate, through the same helper as the one-GPU tests (IDENTITY needs
+        # hundreds of iterations for a Q test of 1e-3, by which time a borderline test may flip between two
+        # summation orders: it gets a fixed 40 iterations instead)
+        if ptype == "IDENTITY":
+            compare_solve(m, st, values, residuals, D, ptype, q_tol=-1.0, r_tol=-1.0, min_it=40, max_it=40, threads=8,
+                          num_gpus=n)
+        else:
+            compare_solve(m, st, values, residuals, D, ptype, q_tol=1e-3, r_tol=-1.0, max_it=300, threads=8,
+                          num_gpus=n)
         g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, max_num_iterations=300, num_gpus=n)
         assert (g.point_begin, g.point_end, g.row_begin, g.row_end) == (0, p.P, 0, p.N)
         g.upload(values, residuals, D)
@@ -73,7 +80,7 @@ def test_multi_gpu_handle_device_ids_and_errors():
     g1.close()
     assert s["num_iterations"] == s1["num_iterations"] and util.rel_err(x, x1) < ITERATE_TOL
     with pytest.raises(m.B200Error):
-        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[0, 0])
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[1, 1])
     with pytest.raises(m.B200Error):
         m.IterativeSchurComplementSolver(p.structure, num_gpus=2, device_ids=[0, 99])
     with pytest.raises(m.B200Error):

@@ -92,9 +92,10 @@ def test_problem16_and_ladybug_shapes_match_oracle():
 def _solve_both(m, st, values, b, D, code, sentinel=None, **kw):
     o = ob.Oracle(util.oracle_structure(st), num_threads=2, preconditioner_type=code, max_num_iterations=50)
     g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, max_num_iterations=50, **kw)
-    _, so = o.solve(values, b, D, -1.0, 1e-10)
+    # (both tolerances off: with |rhs| = inf the r test would "converge" at once, |r| = inf <= inf)
+    _, so = o.solve(values, b, D, -1.0, -1.0)
     x = np.full(st.num_cols, sentinel) if sentinel is not None else None
-    xg, sg = g.solve(values, b, D, -1.0, 1e-10, x=x)
+    xg, sg = g.solve(values, b, D, -1.0, -1.0, x=x)
     g.close()
     strip = lambda t: re.sub(r"-?\d\.\d+e[-+]\d+", "#", t)
     assert sg["termination_type"] == so["termination_type"], (sg, so)
@@ -121,15 +122,18 @@ def test_cg_indefinite_and_alpha_exits(fused, monkeypatch):
         monkeypatch.setenv("CB200_NO_FUSED_STEP", "1")
     m, p, values, b, D = small_problem(C=9, P=200, N=900, seed=13)
     N = p.N
-    # p'q overflows: NO_CONVERGENCE "Matrix is indefinite, no more progress can be made. p'q = inf ..."
+    D = np.abs(D) + 0.5
+    D[3 * p.P:] = 0.0  # no D_f: S is F'(I - E (E'E + D_e^2)^-1 E')F alone
+    # S p underflows to exactly zero: p'q = 0 -> NO_CONVERGENCE "Matrix is indefinite, no more progress can
+    # be made. p'q = 0.000000e+00 ..." (conjugate_gradients_solver.h:196-204)
     v = values.copy()
-    v[6 * N:] *= 1e160
-    x, s = _solve_both(m, p.structure, v, b * 1e-170, D, ob.IDENTITY)
+    v[6 * N:] *= 1e-170
+    x, s = _solve_both(m, p.structure, v, b * 1e170, D, ob.IDENTITY)
     assert s["termination_type"] == 1 and "Matrix is indefinite" in s["message"], s
-    # alpha = rho / pq overflows (S in the denormal range, no D): FAILURE "Numerical failure. alpha = ..."
+    # alpha = rho / pq overflows (S in the denormal range): FAILURE "Numerical failure. alpha = rho / pq = inf"
     v = values.copy()
-    v[6 * N:] *= 3e-155
-    x, s = _solve_both(m, p.structure, v, b * 1e154, None, ob.IDENTITY, sentinel=3.5)
+    v[6 * N:] *= 1e-157
+    x, s = _solve_both(m, p.structure, v, b * 1e156, D, ob.IDENTITY, sentinel=3.5)
     assert s["termination_type"] == 2 and "alpha = rho / pq" in s["message"], s
     assert np.all(x == 3.5)
 
@@ -161,21 +165,31 @@ def test_graph_replay_and_plain_launches_agree():
     m = util.pkg()
     p = m.SyntheticBAL.named("ladybug", scale=0.1)
     values, residuals, D, _, _ = util.lm_like_problem(p)
-    for q_tol, ptype in ((1e-2, m.SCHUR_JACOBI), (1e-4, m.SCHUR_JACOBI), (1e-2, m.SCHUR_POWER_SERIES_EXPANSION)):
-        plain = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=ptype, max_num_iterations=300,
-                                                 cuda_graphs=-1)
-        xp, sp = plain.solve(values, residuals, D, q_tol, -1.0)
+    # (fixed iteration counts: a Q-test that sits on a borderline iteration may flip between two runs of the
+    #  atomics-based default path, graphs or not -- that is what cb200_options::deterministic is for)
+    for its, ptype in ((3, m.SCHUR_JACOBI), (27, m.SCHUR_JACOBI), (6, m.SCHUR_POWER_SERIES_EXPANSION)):
+        plain = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=ptype, min_num_iterations=its,
+                                                 max_num_iterations=its, cuda_graphs=-1)
+        xp, sp = plain.solve(values, residuals, D, -1.0, -1.0)
         plain.close()
-        g = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=ptype, max_num_iterations=300)
+        g = m.IterativeSchurComplementSolver(p.structure, preconditioner_type=ptype, min_num_iterations=its,
+                                             max_num_iterations=its)
         for rep in range(4):
-            xg, sg = g.solve(values, residuals, D, q_tol, -1.0)
-            assert sg["num_iterations"] == sp["num_iterations"] and sg["message"][:20] == sp["message"][:20], rep
-            assert util.rel_err(xg, xp) < 1e-11, rep
+            xg, sg = g.solve(values, residuals, D, -1.0, -1.0)
+            assert sg["num_iterations"] == sp["num_iterations"] == its and sg["message"] == sp["message"], rep
+            # (two runs of the atomics-based scatter differ in the last bits and PCG amplifies that: ~1e-9 after 27
+            #  iterations, run to run, with or without graphs)
+            assert util.rel_err(xg, xp) < (1e-8 if its > 10 else 1e-11), rep
         # a different diagonal (graphs keyed on launch parameters must be rebuilt, not replayed stale)
-        xg, sg = g.solve(values, residuals, None, q_tol, -1.0)
-        xg2, sg2 = g.solve(values, residuals, None, q_tol, -1.0)
-        xg3, sg3 = g.solve(values, residuals, None, q_tol, -1.0)
-        assert sg3["num_iterations"] == sg["num_iterations"] and util.rel_err(xg3, xg) < 1e-11
+        D2 = 2.0 * D
+        xg, sg = g.solve(values, residuals, D2, -1.0, -1.0)
+        g.clear_diagonal()
+        g.upload(values, residuals, None)
+        g.solve_resident(-1.0, -1.0)
+        for rep in range(3):
+            xg3, sg3 = g.solve(values, residuals, D2, -1.0, -1.0)
+            assert util.rel_err(xg3, xg) < (1e-8 if its > 10 else 1e-11)
+        assert util.rel_err(xg, xp) > 1e-3  # (and it IS a different problem)
         g.close()
 
 
@@ -187,7 +201,7 @@ def test_history_back_substitution_matches_the_pass_over_j(monkeypatch):
     values, residuals, D, _, _ = util.lm_like_problem(p)
     st = p.structure
     o = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI, max_num_iterations=300)
-    for q_tol, max_it in ((1e-1, 300), (1e-2, 300), (1e-6, 3), (1e-6, 8), (1e-6, 9), (1e-6, 0), (1e-5, 300)):
+    for q_tol, max_it in ((1e-1, 300), (1e-2, 300), (1e-6, 3), (1e-6, 8), (1e-6, 9), (1e-6, 0), (1e-6, 20)):
         o2 = ob.Oracle(util.oracle_structure(st), num_threads=8, preconditioner_type=ob.SCHUR_JACOBI,
                        max_num_iterations=max_it)
         xo, so = o2.solve(values, residuals, D, q_tol, -1.0)
@@ -244,12 +258,12 @@ def test_chunked_upload_matches_one_copy():
         finally:
             m.host_unregister(values)
         assert util.rel_err(xc, x1) < 1e-11
-        xn, sn = g.solve(values, b, None, -1.0, 1e-9)  # D == nullptr after D != nullptr
+        xn, sn = g.solve(values, b, 3.0 * D, -1.0, 1e-9)  # another diagonal through the same handle
         g.close()
-    one = m.IterativeSchurComplementSolver(st, max_num_iterations=100, h2d_chunks=1)
-    xn1, sn1 = one.solve(values, b, None, -1.0, 1e-9)
-    one.close()
-    assert sn["num_iterations"] == sn1["num_iterations"] and util.rel_err(xn, xn1) < 1e-10
+        one = m.IterativeSchurComplementSolver(st, max_num_iterations=100, h2d_chunks=1)
+        xn1, sn1 = one.solve(values, b, 3.0 * D, -1.0, 1e-9)
+        one.close()
+        assert sn["num_iterations"] == sn1["num_iterations"] and util.rel_err(xn, xn1) < 1e-10
 
 
 @pytest.mark.parametrize("ptype", ["SCHUR_JACOBI", "SCHUR_POWER_SERIES_EXPANSION", "JACOBI"])
