@@ -69,7 +69,9 @@ def bind_to_gpu_numa_node(device):
 
 
 class ClockSampler:
-    """SM clock and throttle reasons sampled (NVML, every 10 ms, own thread) DURING the timed region."""
+    """SM clock and throttle reasons sampled (NVML, every 50 ms, own thread) DURING the timed region. (Not more
+    often: an NVML query holds driver locks for a good fraction of a millisecond, and with several ranks a launch
+    delayed on one of them stalls every GPU at the next exchange.)"""
 
     def __init__(self, device):
         import threading
@@ -103,7 +105,7 @@ class ClockSampler:
                         self.reasons.add(n)
             except Exception:
                 pass
-            self._stop.wait(0.01)
+            self._stop.wait(0.05)
 
     def stop(self):
         if self._thread is not None:

@@ -184,23 +184,22 @@ cg_step_kernel(const CgStepArgs a) {
       const int slot = epoch & 1u;
       if (on) a.peer_q[a.rank][slot * a.slot_stride + o9] = q;
       GridBarrier(st, gen);  // every CTA of this rank has published (and has read the epoch counter)
-      if (threadIdx.x == 0) {
-        if (blockIdx.x == 0) {
-          *a.epoch = epoch;
-          __threadfence_system();
-          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(epoch) : "memory");
-        }
-        for (int rk = 0; rk < a.world; ++rk) {
-          if (rk == a.rank) continue;
-          unsigned int seen;
-          unsigned long long t0, t1;
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-          do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[rk] + slot * 32) : "memory");
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }  // never hang the GPU
-          } while (seen != epoch);
-        }
+      if (threadIdx.x == 0 && blockIdx.x == 0) {
+        *a.epoch = epoch;
+        __threadfence_system();
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.peer_flag[a.rank] + slot * 32), "r"(epoch) : "memory");
+      }
+      // one polling thread per peer: the NVLink round trips of the world - 1 flags overlap instead of adding up
+      if (threadIdx.x < a.world && threadIdx.x != a.rank) {
+        const int rk = threadIdx.x;
+        unsigned int seen;
+        unsigned long long t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        do {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(a.peer_flag[rk] + slot * 32) : "memory");
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+          if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }  // never hang the GPU
+        } while (seen != epoch);
       }
       __syncthreads();
       if (on) {
@@ -347,24 +346,19 @@ peer_allreduce_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgSt
       __threadfence_system();
       asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.flag[p.rank] + slot * 32), "r"(epoch) : "memory");
     }
-    for (int r = 0; r < p.world; ++r) {
-      if (r == p.rank) continue;
-      unsigned int seen;
-      unsigned long long t0, t1;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-      do {
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[r] + slot * 32) : "memory");
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }
-      } while (seen != epoch);
-    }
-    // (own flag: the sum below also reads this rank's slot, complete only when every CTA has published)
-    if (gridDim.x > 1) {
-      unsigned int seen;
-      do {
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[p.rank] + slot * 32) : "memory");
-      } while (seen != epoch && !*reinterpret_cast<volatile int*>(&st->peer_timeout));
-    }
+  }
+  // one polling thread per rank (own flag included: the sum below also reads this rank's slot, complete only
+  // when every CTA of this grid has published): the NVLink round trips overlap instead of adding up
+  if (threadIdx.x < p.world && (threadIdx.x != p.rank || gridDim.x > 1)) {
+    const int r = threadIdx.x;
+    unsigned int seen;
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    do {
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.flag[r] + slot * 32) : "memory");
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }
+    } while (seen != epoch);
   }
   __syncthreads();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {

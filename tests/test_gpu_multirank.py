@@ -24,13 +24,19 @@ def _worker(rank, world, uid, ptype, out):
     g.close()
 
 
+def _worlds():
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    return sorted({2, n}) if n >= 2 else [2]
+
+
+@pytest.mark.parametrize("world", _worlds())
 @pytest.mark.parametrize("ptype", [2, 3])
-def test_two_gpu_solve_matches_oracle(ptype):
-    if torch.cuda.device_count() < 2:
+def test_two_gpu_solve_matches_oracle(ptype, world):
+    """world = 2 and world = every GPU of the box (8 on the scaling box)."""
+    if torch.cuda.device_count() < world:
         pytest.skip("needs 2 GPUs")
     from oracle import binding as ob
     m = util.pkg()
-    world = 2
     uid = m.nccl_unique_id()
     ctx = mp.get_context("spawn")
     out = ctx.Manager().dict()
