@@ -436,7 +436,7 @@ int CreateShard(const cb200_structure* structure, const cb200_options& o, InProc
   TRY(DeviceAlloc(s, &s->d_Df, nv));
   TRY(DeviceAlloc(s, &s->d_ete_inv, Pl * 6));
   TRY(DeviceAlloc(s, &s->d_ete9, Pl * 9));
-  TRY(DeviceAlloc(s, &s->d_weights, Nl * 3));
+  TRY(DeviceAlloc(s, &s->d_weights, Nl * kWeightStride));
   TRY(DeviceAlloc(s, &s->d_chunk_partial, (size_t)s->num_chunks * 45));
   TRY(DeviceAlloc(s, &s->d_upper, (size_t)s->C * 45));
   TRY(DeviceAlloc(s, &s->d_dup_blocks, (size_t)s->C * 81));

@@ -73,12 +73,22 @@ camera_block_kernel(const double* __restrict__ F, const double* __restrict__ wei
       if (r >= 0) cp_async16(dst + o * kChunkSlot + 16 * pc, F + (size_t)r * 18 + 2 * pc);
     }
     if (WEIGHTED) {
+      if (kWeightStride == 4) {  // one aligned 32-byte sector per row: two 16-byte pieces
 #pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const int idx = j * 32 + lane;
-        const int o = idx / 3, pc = idx - 3 * o;
-        const int r = __shfl_sync(0xffffffffu, r_own, o);
-        if (r >= 0) cp_async8(dst + o * kChunkSlot + 144 + 8 * pc, weights + (size_t)r * 3 + pc);
+        for (int j = 0; j < 2; ++j) {
+          const int idx = j * 32 + lane;
+          const int o = idx >> 1, pc = idx & 1;
+          const int r = __shfl_sync(0xffffffffu, r_own, o);
+          if (r >= 0) cp_async16(dst + o * kChunkSlot + 144 + 16 * pc, weights + (size_t)r * 4 + 2 * pc);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+          const int idx = j * 32 + lane;
+          const int o = idx / 3, pc = idx - 3 * o;
+          const int r = __shfl_sync(0xffffffffu, r_own, o);
+          if (r >= 0) cp_async8(dst + o * kChunkSlot + 144 + 8 * pc, weights + (size_t)r * 3 + pc);
+        }
       }
     }
     cp_async_commit();

@@ -23,6 +23,14 @@ namespace cb200 {
 
 constexpr int kTileObs = 32;  // rows per tile of the fused per-point kernels: one lane each
 constexpr int kTilePoints = 16;  // points (= (E'E)^-1 blocks staged) per tile; real tracks have >= 2 rows
+// doubles per row of the Schur-Jacobi weights array (w00, w01, w11 [, pad]). 4 would give the camera-major gather of
+// camera_block_kernel one aligned 32-byte sector per row instead of 1.5 on average; measured (round 2, Venice shape,
+// same box): camera blocks 250.0 -> 250.9 us, E'E / rhs pass 283.5 -> 285.9 us (8 more bytes written per row). The
+// gather is not limited by those bytes; 3 stays.
+#ifndef CB200_WEIGHT_STRIDE
+#define CB200_WEIGHT_STRIDE 3
+#endif
+constexpr int kWeightStride = CB200_WEIGHT_STRIDE;
 constexpr int kChunkedPointRows = 256;  // points of 33..256 rows run as chunk tiles inside the stream kernel
 // flags in TileMeta::np above the point count (low 8 bits)
 constexpr int kTileKindShift = 8;        // bits 8-9: 0 whole points, 1 first-pass chunk, 2 second-pass chunk

@@ -418,10 +418,16 @@ point_stream_kernel(const StreamArgs a) {
       const double g11 = Ei[3] * c6[1] + Ei[4] * c6[3] + Ei[5] * c6[4];
       const double g12 = Ei[3] * c6[2] + Ei[4] * c6[4] + Ei[5] * c6[5];
       if (active) {
-        double* w = a.weights + (size_t)(r0 + lane) * 3;
-        w[0] = 1.0 - (g00 * Ei[0] + g01 * Ei[1] + g02 * Ei[2]);
-        w[1] = -(g00 * Ei[3] + g01 * Ei[4] + g02 * Ei[5]);
-        w[2] = 1.0 - (g10 * Ei[3] + g11 * Ei[4] + g12 * Ei[5]);
+        double* w = a.weights + (size_t)(r0 + lane) * kWeightStride;
+        const double w00 = 1.0 - (g00 * Ei[0] + g01 * Ei[1] + g02 * Ei[2]);
+        const double w01 = -(g00 * Ei[3] + g01 * Ei[4] + g02 * Ei[5]);
+        const double w11 = 1.0 - (g10 * Ei[3] + g11 * Ei[4] + g12 * Ei[5]);
+        if (kWeightStride == 4) {
+          reinterpret_cast<double2*>(w)[0] = make_double2(w00, w01);
+          reinterpret_cast<double2*>(w)[1] = make_double2(w11, 0.0);
+        } else {
+          w[0] = w00; w[1] = w01; w[2] = w11;
+        }
       }
     }
     __syncwarp();
@@ -555,7 +561,7 @@ point_long_kernel(const StreamArgs a, const int* __restrict__ long_points,
         g0[j] = Ei[0] * c[j] + Ei[1] * c[3 + j] + Ei[2] * c[6 + j];
         g1[j] = Ei[3] * c[j] + Ei[4] * c[3 + j] + Ei[5] * c[6 + j];
       }
-      double* w = a.weights + (size_t)r * 3;
+      double* w = a.weights + (size_t)r * kWeightStride;
       w[0] = 1.0 - (g0[0] * Ei[0] + g0[1] * Ei[1] + g0[2] * Ei[2]);
       w[1] = -(g0[0] * Ei[3] + g0[1] * Ei[4] + g0[2] * Ei[5]);
       w[2] = 1.0 - (g1[0] * Ei[3] + g1[1] * Ei[4] + g1[2] * Ei[5]);
