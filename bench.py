@@ -190,6 +190,7 @@ def main():
     ap.add_argument("--no-cusparse", action="store_true", help="skip the cuSPARSE CSR comparison of S*x")
     ap.add_argument("--no-explicit", action="store_true",
                     help="skip the use_explicit_schur_complement comparison (SURVEY 8(f) row 3)")
+    ap.add_argument("--no-fixed", action="store_true", help="skip the fixed-work PCG arm (short runs under ncu)")
     ap.add_argument("--lm-iterations", type=int, default=10)
     ap.add_argument("--precond", default="schur_jacobi", choices=["schur_jacobi", "spse", "jacobi", "identity"])
     args = ap.parse_args()
@@ -301,18 +302,19 @@ def main():
 
     # ---- fixed-work PCG (SURVEY 8(d) "Solver settings": min = max = K iterations, q / r tests off) ----------
     g.set_iterations(FIXED_PCG, FIXED_PCG)
-    for _ in range(2):
+    for _ in range(0 if args.no_fixed else 2):
         g.solve_resident(-1.0, -1.0)
     barrier()
     fixed_ms, fixed_its = 0.0, 0
-    for _ in range(3):
+    for _ in range(1 if args.no_fixed else 3):
         sf = g.solve_resident(-1.0, -1.0)
         fixed_ms += sf["total_ms"]
         fixed_its += sf["num_iterations"]
     fixed_ms = max_over_ranks(fixed_ms)
     g.set_iterations(0, MAX_PCG)
-    pcg_fixed = {"iterations_per_solve": fixed_its / 3, "ms_per_solve": fixed_ms / 3,
-                 "ms_per_pcg_iteration": (fixed_ms - 3 * (s["setup_ms"])) / max(fixed_its, 1),
+    nfix = 1 if args.no_fixed else 3
+    pcg_fixed = {"iterations_per_solve": fixed_its / nfix, "ms_per_solve": fixed_ms / nfix,
+                 "ms_per_pcg_iteration": (fixed_ms - nfix * (s["setup_ms"])) / max(fixed_its, 1),
                  "note": "3 solves with min = max = %d PCG iterations, q / r tests off; the rate counts the whole "
                          "solve (setup and back substitution included)" % FIXED_PCG}
 

@@ -26,11 +26,21 @@ def main():
     ap.add_argument("--nrep", type=int, nargs="+", default=[0])
     ap.add_argument("--pcg", type=int, default=0, help="time a solve with exactly this many PCG iterations")
     ap.add_argument("--period", type=int, default=0)
+    ap.add_argument("--lm-values", action="store_true",
+                    help="the bench's problem (Snavely Jacobian, Jacobi-scaled, LM diagonal) instead of N(0,1) values")
+    ap.add_argument("--solves-first", type=int, default=0, help="run this many LM-shaped solves before timing the ops")
     args = ap.parse_args()
     pkg = importlib.import_module("ceres-solver-ceres-solver_b200")
-    p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, geometry=False)
-    values, b, D = p.random_values(1)
-    D = np.abs(D) + 1.0
+    if args.lm_values:
+        p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, rotation_sigma=2e-3, translation_sigma=1.0, point_sigma=1.0)
+        cost, b, values = p.evaluate()
+        jscale = 1.0 / (1.0 + np.sqrt(p.squared_column_norm(values)))
+        p.scale_columns(values, jscale)
+        D = np.sqrt(np.clip(p.squared_column_norm(values), 1e-6, 1e32) / 1e4)
+    else:
+        p = pkg.SyntheticBAL.named(args.shape, scale=args.scale, geometry=False)
+        values, b, D = p.random_values(1)
+        D = np.abs(D) + 1.0
     N, P, C = p.N, p.P, p.C
     bytes_sx = 192 * N + 4 * N + 4 * P + 72 * P + 144 * C
     for nrep in args.nrep:
@@ -38,6 +48,8 @@ def main():
                                                y_replicas=nrep, status_check_period=args.period)
         g.upload(values, b, D)
         g.isc_init()
+        for _ in range(args.solves_first):
+            g.solve_resident(1e-2, -1.0)
         for op in args.op:
             ms, launches = g.time_op(op, warmup=args.warmup, iters=args.iters)
             print(f"nrep {nrep} op {op}: {ms:.4f} ms/launch-group ({launches} launches); "
