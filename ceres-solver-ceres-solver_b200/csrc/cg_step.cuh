@@ -309,6 +309,53 @@ cg_step_kernel(const CgStepArgs a) {
 namespace cb200 {
 
 // ----------------------------------------------------------------------------
+// One term of the power-series preconditioner (power_series_expansion_preconditioner.cc:57-82) after its pass
+// over the Jacobian: fold the accumulators (q = F'E (E'E)^-1 E'F * previous term), term = (F'F + D_f^2)^-1 q,
+// y += term, and the padded copy the next pass multiplies -- one kernel instead of fold + block multiply + axpy +
+// pad. FIRST: the zeroth term y = (F'F + D_f^2)^-1 x. Same thread layout as cg_step_kernel (a CTA owns 14
+// cameras); no grid-wide dependency, so a plain launch. q_in non-null: q arrives folded (several GPUs,
+// deterministic mode).
+// ----------------------------------------------------------------------------
+template <bool FIRST>
+__global__ void __launch_bounds__(kStepThreads)
+pse_term_kernel(const int* done, const double* __restrict__ blocks, const double* __restrict__ q_in,
+                double* __restrict__ yrep, int nrep, int rep_stride, int C, double* __restrict__ y,
+                double* __restrict__ term_out, double* __restrict__ x10) {
+  if (done != nullptr && *done) return;
+  __shared__ double sQ[kStepThreads];
+  const int local = threadIdx.x / 9;
+  const int i = threadIdx.x - 9 * local;
+  const int c = blockIdx.x * kStepCams + local;
+  const bool on = local < kStepCams && c < C;
+  const size_t o9 = (size_t)c * 9 + i, o10 = (size_t)c * 10 + i;
+  double q = 0.0;
+  double Brow[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) Brow[k] = 0.0;
+  if (on) {
+    const double* B = blocks + (size_t)c * 81 + 9 * i;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) Brow[k] = __ldg(B + k);
+    if (q_in != nullptr) {
+      q = q_in[o9];
+    } else {
+      for (int rep = 0; rep < nrep; ++rep) q += __ldcg(yrep + (size_t)rep * rep_stride + o10);
+      for (int rep = 0; rep < nrep; ++rep) yrep[(size_t)rep * rep_stride + o10] = 0.0;
+    }
+  }
+  sQ[threadIdx.x] = q;
+  __syncthreads();
+  if (!on) return;
+  const double* qc = sQ + 9 * local;
+  double t = 0.0;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) t += Brow[k] * qc[k];
+  y[o9] = FIRST ? t : y[o9] + t;
+  term_out[o9] = t;
+  x10[o10] = t;
+}
+
+// ----------------------------------------------------------------------------
 // The same exchange for the per-solve sums (reduced rhs, preconditioner blocks, the
 // scalars of the trust-region loop): buf[0..n) <- sum (or max) over ranks, in rank
 // order, through the peer-mapped buffers. ONE plain launch of <= 64 CTAs: every CTA
