@@ -15,7 +15,7 @@ LIB_LM = os.path.join(HERE, "libceres_b200_lm.so")
 
 _CUDA_SRC = ["c_api.cu", "c_api_solve.inc", "c_api_entry.inc", "c_api_lm.inc", "lm_kernels.cuh", "snavely_model.h", "kernels.cuh", "camera_kernels.cuh",
              "cg_kernels.cuh", "cg_step.cuh", "stream_kernels.cuh", "solver_state.h", "flatten.h",
-             "c_api_explicit.inc", "explicit_kernels.cuh", "explicit_plan.h"]
+             "c_api_explicit.inc", "explicit_kernels.cuh", "explicit_plan.h", "multi_gpu.h"]
 
 
 def _stale(out, srcs):

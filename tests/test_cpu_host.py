@@ -222,3 +222,14 @@ def test_explicit_plan_invariants_host_only(tmp_path):
     assert int(kv["cells"]) > 37 and int(kv["dup_pairs"]) > 0 and int(kv["items"]) > 400, out
     for k in ("bad_structure", "bad_transpose", "bad_pairs", "bad_order", "bad_items"):
         assert kv[k] == "0", out
+
+
+def test_inprocess_group_rendezvous(tmp_path):
+    """The host rendezvous of a multi-GPU handle's shards (InProcGroup, csrc/multi_gpu.h) under real threads:
+    barriers in lock step, rank-ordered sums bit-identical on every shard, Abort releases waiting shards."""
+    import subprocess
+    exe = str(tmp_path / "inproc_group_driver")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", "-o", exe,
+                    os.path.join(util.ROOT, "tests", "cpp", "inproc_group_driver.cc")], check=True)
+    out = subprocess.run([exe], check=True, capture_output=True, text=True, timeout=60).stdout
+    assert out.strip() == "order_errors=0 differing=0 value_ok=1 released=2", out
