@@ -69,7 +69,18 @@ __device__ __forceinline__ void GridBarrier(CgState* st, unsigned int& gen) {
       __threadfence();
       atomicExch(&st->bar_flag, gen + 1);
     } else {
-      while (*reinterpret_cast<volatile unsigned int*>(&st->bar_flag) == gen) {}
+      // (never hang the GPU: a CTA that is not co-resident -- impossible under a cooperative launch -- or a
+      //  faulted sibling would otherwise spin here for ever; 4 s, checked every 4096 polls)
+      unsigned long long t0 = 0;
+      unsigned int polls = 0;
+      while (*reinterpret_cast<volatile unsigned int*>(&st->bar_flag) == gen) {
+        if ((++polls & 4095u) == 0u) {
+          unsigned long long t1;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+          if (t0 == 0) t0 = t1;
+          else if (t1 - t0 > kPeerTimeoutNs) { atomicExch(&st->peer_timeout, 1); break; }
+        }
+      }
     }
     __threadfence();
   }
@@ -203,9 +214,16 @@ cg_step_kernel(const CgStepArgs a) {
       }
       __syncthreads();
       if (on) {
-        q = 0.0;
-        for (int rk = 0; rk < a.world; ++rk)  // rank order: the same sum, bit for bit, on every rank
-          q += __ldcg(a.peer_q[rk] + slot * a.slot_stride + o9);
+        // all peers' values requested at once (independent loads: one NVLink round trip, not world of them),
+        // then added in rank order: the same sum, bit for bit, on every rank
+        double v[kMaxPeers];
+#pragma unroll
+        for (int rk = 0; rk < kMaxPeers; ++rk)
+          v[rk] = rk < a.world ? __ldcg(a.peer_q[rk] + slot * a.slot_stride + o9) : 0.0;
+        q = v[0];
+#pragma unroll
+        for (int rk = 1; rk < kMaxPeers; ++rk)
+          if (rk < a.world) q += v[rk];
       }
     }
     // + D_f^2 * (the multiplied vector): p, or x in the second half of a reset
@@ -409,11 +427,13 @@ peer_allreduce_kernel(const PeerRefs p, double* __restrict__ buf, size_t n, CgSt
   }
   __syncthreads();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    double s = __ldcg(p.base[0] + slot * p.slot_stride + i);
-    for (int r = 1; r < p.world; ++r) {  // rank order: bit-identical on every rank
-      const double v = __ldcg(p.base[r] + slot * p.slot_stride + i);
-      s = MAX ? fmax(s, v) : s + v;
-    }
+    double v[kMaxPeers];  // independent loads first, then the rank-ordered sum: bit-identical on every rank
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r) v[r] = r < p.world ? __ldcg(p.base[r] + slot * p.slot_stride + i) : 0.0;
+    double s = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r)
+      if (r < p.world) s = MAX ? fmax(s, v[r]) : s + v[r];
     buf[i] = s;
   }
   __syncthreads();

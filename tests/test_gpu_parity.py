@@ -460,9 +460,9 @@ def test_bundle_adjuster_cli_matches_reference_loop(tmp_path, explicit):
     assert open(tmp_path / "out.ply").readline().strip() == "ply"
 
 
-def test_host_registered_buffers_upload_faster_and_solve_the_same():
+def test_host_registered_buffers_solve_the_same():
     """cb200_host_register (what the adapter does to BlockSparseMatrix::values()): the same solve from a
-    page-locked numpy buffer, with the H2D copy at least as fast as from pageable memory."""
+    page-locked numpy buffer. (The copy rates are a bench.py matter: no timing assertions in this suite.)"""
     m = util.pkg()
     p = m.SyntheticBAL.named("ladybug")
     values, residuals, D, _, _ = util.lm_like_problem(p)
@@ -477,7 +477,6 @@ def test_host_registered_buffers_upload_faster_and_solve_the_same():
     finally:
         m.host_unregister(values)
     assert s1["num_iterations"] == s0["num_iterations"] and util.rel_err(x1, x0) < 1e-11  # (atomics: not bitwise)
-    assert s1["h2d_ms"] <= 1.05 * s0["h2d_ms"], (s0["h2d_ms"], s1["h2d_ms"])
     g.close()
 
 
