@@ -9,5 +9,6 @@ import it with importlib.import_module("ceres-solver-ceres-solver_b200").
 from . import _build  # noqa: F401
 from .solver import (IDENTITY, JACOBI, SCHUR_JACOBI, SCHUR_POWER_SERIES_EXPANSION,  # noqa: F401
                      TERMINATION, B200Error, BlockStructure, IterativeSchurComplementSolver,
-                     nccl_unique_id, shard_plan, explicit_plan, host_register, host_unregister)
+                     nccl_unique_id, shard_plan, explicit_plan, host_register, host_unregister,
+                     block_diagonal_apply_static)
 from .bal import SHAPES, BALFile, SyntheticBAL  # noqa: F401

@@ -122,6 +122,7 @@ SYMBOLS = {
     "cb200_schur_jacobi_update": (ctypes.c_int, [_H, ctypes.c_int, _dp]),
     "cb200_schur_jacobi_apply": (ctypes.c_int, [_H, _dp, _dp]),
     "cb200_pse_apply": (ctypes.c_int, [_H, ctypes.c_int, ctypes.c_double, _dp, _dp]),
+    "cb200_block_diagonal_apply_static": (ctypes.c_int, [_dp, _dp, _dp, ctypes.c_int]),
     "cb200_time_op": (ctypes.c_int, [_H, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                      ctypes.POINTER(ctypes.c_float), _ip]),
     "cb200_bal_attach": (ctypes.c_int, [_H, _dp]),
@@ -450,6 +451,12 @@ class IterativeSchurComplementSolver:
         ms, n = ctypes.c_float(), ctypes.c_int()
         _check(self.L.cb200_time_op(self.h, op, warmup, iters, ctypes.byref(ms), ctypes.byref(n)))
         return ms.value, n.value
+
+
+def block_diagonal_apply_static(blocks, x, y):
+    """y += B x through cb200_block_diagonal_apply_static (no handle, no allocation; <= 16384 blocks)."""
+    _check(lib().cb200_block_diagonal_apply_static(_d(blocks), _d(x), _d(y), len(x) // 9))
+    return y
 
 
 def shard_plan(structure, world_size):

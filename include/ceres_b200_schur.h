@@ -259,6 +259,16 @@ int cb200_schur_jacobi_apply(cb200_solver* s, const double* x, double* y);
 int cb200_pse_apply(cb200_solver* s, int max_num_spse_iterations,
                     double spse_tolerance, const double* x, double* y);
 
+/* y += B x for a block-diagonal matrix of num_blocks row-major 9x9 blocks (host pointers: blocks 81 n, x 9 n,
+ * y 9 n) -- what cb200_schur_jacobi_apply computes, WITHOUT a solver handle and WITHOUT any allocation: no
+ * cudaMalloc / cudaFree / allocating library call, so it can be used where those are forbidden. It has no
+ * counterpart in the reference. The operands are staged in
+ * one file-scope static device array of 99 * 16384 doubles (12.98 MB, held by every GPU that loads the library
+ * until the process exits): num_blocks > 16384 is rejected with CB200_ERR_INVALID_ARGUMENT. Runs on the current
+ * device, legacy default stream, synchronously. All calls share the array, which keeps the last call's contents
+ * (every call overwrites what it reads; nothing needs to start at zero): calls that overlap on the GPU race. */
+int cb200_block_diagonal_apply_static(const double* blocks, const double* x, double* y, int num_blocks);
+
 /* Device-resident timing of one op (CUDA events on the solver's stream, `iters`
  * back-to-back launches after `warmup`); ms_out = average per launch.
  * op: 0 S*x (isc multiply), 1 EtE inverse build, 2 rhs, 3 Schur-Jacobi build,
