@@ -131,6 +131,7 @@ struct cb200_solver {
   // CUDA graphs of the launch sequences of a solve, by sequence key; any change of a launch parameter
   // (diagonal on / off, trace, model pointer ...) bumps graph_config and drops them
   bool graphs_ok = false;
+  int last_iterations = 0;                    // PCG iterations of the previous solve (length of the next first batch)
   long long graph_sig = 0;
   std::map<long long, cudaGraphExec_t> graphs;
   std::map<long long, int> graph_launches;    // kernels inside each graph
