@@ -233,3 +233,24 @@ def test_inprocess_group_rendezvous(tmp_path):
                     os.path.join(util.ROOT, "tests", "cpp", "inproc_group_driver.cc")], check=True)
     out = subprocess.run([exe], check=True, capture_output=True, text=True, timeout=60).stdout
     assert out.strip() == "order_errors=0 differing=0 value_ok=1 released=2", out
+
+
+def test_round2_option_validation_needs_no_device():
+    """cb200_options added in round 2 are validated before any device work: num_gpus excludes world_size > 1,
+    bounds on num_gpus / h2d_chunks, deterministic excludes the explicit matrix. (Without a GPU a VALID
+    configuration then fails with CB200_ERR_CUDA: there is no CPU fallback.)"""
+    m = util.pkg()
+    p = m.SyntheticBAL(5, 20, 60, geometry=False)
+    with pytest.raises(m.B200Error, match="excludes world_size"):
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=2, world_size=2, rank=0, nccl_unique_id=b"\0" * 128)
+    with pytest.raises(m.B200Error, match="bad num_gpus"):
+        m.IterativeSchurComplementSolver(p.structure, num_gpus=17)
+    with pytest.raises(m.B200Error, match="bad h2d_chunks"):
+        m.IterativeSchurComplementSolver(p.structure, h2d_chunks=1000)
+    with pytest.raises(m.B200Error, match="deterministic mode covers the implicit operator only"):
+        m.IterativeSchurComplementSolver(p.structure, deterministic=True, use_explicit_schur_complement=True)
+    if not util.has_gpu():
+        with pytest.raises(m.B200Error, match="cb200 error -3"):
+            m.IterativeSchurComplementSolver(p.structure, num_gpus=2)
+        with pytest.raises(m.B200Error, match="cb200 error -3"):
+            m.block_diagonal_apply_static(np.zeros(81), np.zeros(9), np.zeros(9))
