@@ -112,8 +112,8 @@ typedef struct cb200_options {
   int deterministic;          /* 1 = bitwise-repeatable solves: the camera scatter F'w of every
                                  product is summed per camera in a fixed order (a second,
                                  camera-major pass) instead of FP64 atomics, so borderline
-                                 convergence tests cannot flip between runs. About 2x the time
-                                 per product. Implicit operator only.                        */
+                                 convergence tests cannot flip between runs. 1.8x the time per
+                                 product (measured, Venice shape). Implicit operator only.                        */
   int cuda_graphs;            /* 0 = default (on): the launch sequence of a solve is captured once
                                  and replayed as CUDA graphs; -1 = off (plain stream launches)  */
   int h2d_chunks;             /* 0 = default (16): cb200_solve copies the Jacobian in this many

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--nrep", type=int, nargs="+", default=[0])
     ap.add_argument("--pcg", type=int, default=0, help="time a solve with exactly this many PCG iterations")
     ap.add_argument("--period", type=int, default=0)
+    ap.add_argument("--deterministic", action="store_true", help="cb200_options::deterministic")
     ap.add_argument("--lm-values", action="store_true",
                     help="the bench's problem (Snavely Jacobian, Jacobi-scaled, LM diagonal) instead of N(0,1) values")
     ap.add_argument("--solves-first", type=int, default=0, help="run this many LM-shaped solves before timing the ops")
@@ -45,7 +46,8 @@ def main():
     bytes_sx = 192 * N + 4 * N + 4 * P + 72 * P + 144 * C
     for nrep in args.nrep:
         g = pkg.IterativeSchurComplementSolver(p.structure, preconditioner_type=args.precond, max_num_iterations=50,
-                                               y_replicas=nrep, status_check_period=args.period)
+                                               y_replicas=nrep, status_check_period=args.period,
+                                               deterministic=args.deterministic)
         g.upload(values, b, D)
         g.isc_init()
         for _ in range(args.solves_first):
