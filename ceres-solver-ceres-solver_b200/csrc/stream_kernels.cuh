@@ -31,6 +31,23 @@
 
 namespace cb200 {
 
+// pipeline depth and minimum resident CTAs per SM of the E'E / rhs (BUILD) pass and of the S*x pass (the other
+// modes keep 2 / 3); macros so that tools/build_variant.py can A/B them
+#ifndef CB200_STAGES_BUILD
+#define CB200_STAGES_BUILD 1
+#endif
+#ifndef CB200_MINCTAS_BUILD
+#define CB200_MINCTAS_BUILD 4
+#endif
+#ifndef CB200_STAGES_SX
+#define CB200_STAGES_SX 1
+#endif
+// S*x with ONE data stage and the tile side-band (TileMeta) in its own ring of two slots: the camera ids of the
+// NEXT tile are there one tile ahead (the x gather needs them), while E / F / (E'E)^-1 use a single stage that is
+// refilled as soon as the lanes hold their blocks in registers: 10 KB instead of 17 KB per warp -> 16 warps per SM
+#ifndef CB200_SX_META_RING
+#define CB200_SX_META_RING 1
+#endif
 constexpr int kStreamWarps = 4;
 constexpr int kStreamThreads = kStreamWarps * 32;
 constexpr int kMetaBytes = (int)sizeof(TileMeta);
@@ -80,18 +97,26 @@ template <int MODE, bool BUILD>
 struct StreamLayout {
   static constexpr bool kUsesB = (MODE == kModeRhs || MODE == kModeBack);
   static constexpr bool kLoadsInv = !BUILD;
-  static constexpr int kStages = 2;
+  // modes that take the meta ring + single data stage: S*x and the power-series product (CB200_SX_META_RING >= 1),
+  // back substitution too (>= 2)
+  static constexpr bool kRingMode = !BUILD && ((CB200_SX_META_RING >= 1 && (MODE == 0 || MODE == 1)) ||
+                                               (CB200_SX_META_RING >= 2 && MODE == 3));
+  static constexpr int kStages = BUILD ? CB200_STAGES_BUILD : (kRingMode ? CB200_STAGES_SX : 2);
   // per stage (every offset a multiple of 16 bytes)
   static constexpr int kOffE = 0;
   static constexpr int kOffF = kOffE + kTileObs * 48;
   static constexpr int kOffMeta = kOffF + kTileObs * 144;
-  static constexpr int kOffInv = kOffMeta + kMetaBytes;
+  static constexpr bool kMetaRing = kRingMode;
+  static constexpr int kMetaSlots = kMetaRing ? 2 : 0;
+  static constexpr int kOffInv = kOffMeta + (kMetaRing ? 0 : kMetaBytes);
   static constexpr int kOffB = kOffInv + (kLoadsInv ? kTilePoints * 48 : 0);
   static constexpr int kStageBytes = kOffB + (kUsesB ? kTileObs * 16 : 0);
-  // per warp: stages, then the 32 x 10 transposition scratch, then the barriers
-  static constexpr int kOffX = kStages * kStageBytes;
+  // per warp: stages, (the meta ring,) then the 32 x 10 transposition scratch, then the barriers
+  static constexpr int kOffMetaRing = kStages * kStageBytes;
+  static constexpr int kOffX = kOffMetaRing + kMetaSlots * kMetaBytes;
   static constexpr int kOffBars = kOffX + 320 * 8;
-  static constexpr int kOffCarry = kOffBars + 16 * ((kStages * 8 + 15) / 16);  // 18 doubles, long points only
+  static constexpr int kNumBars = kStages + kMetaSlots;
+  static constexpr int kOffCarry = kOffBars + 16 * ((kNumBars * 8 + 15) / 16);  // 18 doubles, long points only
   static constexpr int kWarpBytes = kOffCarry + 144;
   static constexpr int kSmemBytes = kStreamWarps * kWarpBytes;
 };
@@ -100,15 +125,21 @@ template <typename L>
 __device__ __forceinline__ void IssueTile(const StreamArgs& a, int t, const int4 h /* r0, n, p0, np */,
                                           unsigned char* st, uint64_t* bar, uint64_t stream_policy) {
   const bool use_b = L::kUsesB && a.b != nullptr;
-  const uint32_t bytes = (uint32_t)h.y * 192u + (uint32_t)kMetaBytes +
+  const uint32_t bytes = (uint32_t)h.y * 192u + (L::kMetaRing ? 0u : (uint32_t)kMetaBytes) +
                          (L::kLoadsInv ? (uint32_t)(h.w & 255) * 48u : 0u) + (use_b ? (uint32_t)h.y * 16u : 0u);
   mbar_expect_tx(bar, bytes);
-  bulk_g2s(st + L::kOffMeta, a.tiles + t, (uint32_t)kMetaBytes, bar);
+  if (!L::kMetaRing) bulk_g2s(st + L::kOffMeta, a.tiles + t, (uint32_t)kMetaBytes, bar);
   // Jacobian blocks and b are read once per pass: first in line for eviction
   bulk_g2s_hint(st + L::kOffE, a.E + (size_t)h.x * 6, (uint32_t)h.y * 48u, bar, stream_policy);
   bulk_g2s_hint(st + L::kOffF, a.F + (size_t)h.x * 18, (uint32_t)h.y * 144u, bar, stream_policy);
   if (L::kLoadsInv) bulk_g2s(st + L::kOffInv, a.ete_inv + (size_t)h.z * 6, (uint32_t)(h.w & 255) * 48u, bar);
   if (use_b) bulk_g2s_hint(st + L::kOffB, a.b + (size_t)h.x * 2, (uint32_t)h.y * 16u, bar, stream_policy);
+}
+
+// (meta ring) the side-band record of tile t into a ring slot
+__device__ __forceinline__ void IssueMeta(const StreamArgs& a, int t, unsigned char* slot, uint64_t* bar) {
+  mbar_expect_tx(bar, (uint32_t)kMetaBytes);
+  bulk_g2s(slot, a.tiles + t, (uint32_t)kMetaBytes, bar);
 }
 
 // Tile header (r0, n, p0, np). volatile asm: the compiler must keep the value in
@@ -139,7 +170,7 @@ __device__ __forceinline__ double SegScan(double v, const SegMask& k) {
 }
 
 template <int MODE, bool BUILD, bool DET = false>
-__global__ void __launch_bounds__(kStreamThreads, 3)
+__global__ void __launch_bounds__(kStreamThreads, BUILD ? CB200_MINCTAS_BUILD : 3)
 point_stream_kernel(const StreamArgs a) {
   using L = StreamLayout<MODE, BUILD>;
   static_assert(!BUILD || MODE == kModeRhs, "the E'E build rides on the rhs pass");
@@ -171,10 +202,12 @@ point_stream_kernel(const StreamArgs a) {
   int4 hnext = make_int4(0, 0, 0, 0);
   const uint64_t stream_policy = policy_evict_first();
   if (lane == 0) {
-    for (int s = 0; s < L::kStages; ++s) mbar_init(full + s, 1);
+    for (int s = 0; s < L::kNumBars; ++s) mbar_init(full + s, 1);
     for (int s = 0; s < L::kStages && t_begin + s < t_end; ++s)
       IssueTile<L>(a, t_begin + s, LoadHeader(a.tiles + t_begin + s),
                    wsm + s * L::kStageBytes, full + s, stream_policy);
+    for (int k = 0; k < L::kMetaSlots && t_begin + k < t_end; ++k)
+      IssueMeta(a, t_begin + k, wsm + L::kOffMetaRing + k * kMetaBytes, full + L::kStages + k);
     if (t_begin + L::kStages < t_end) hnext = LoadHeader(a.tiles + t_begin + L::kStages);
   }
   __syncwarp();
@@ -197,8 +230,13 @@ point_stream_kernel(const StreamArgs a) {
     }
   };
   if (MODE != kModeRhs) {
-    mbar_wait(full + 0, 0);
-    gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMeta));
+    if (L::kMetaRing) {
+      mbar_wait(full + L::kStages, 0);
+      gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMetaRing));
+    } else {
+      mbar_wait(full + 0, 0);
+      gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMeta));
+    }
   }
 
   // carry of a long point across its chunk tiles: kept in shared memory (touched by chunk
@@ -215,7 +253,10 @@ point_stream_kernel(const StreamArgs a) {
     const int s = i % L::kStages;
     unsigned char* st = wsm + s * L::kStageBytes;
     mbar_wait(full + s, (i / L::kStages) & 1);
-    const TileMeta* m = reinterpret_cast<const TileMeta*>(st + L::kOffMeta);
+    if (L::kMetaRing) mbar_wait(full + L::kStages + (i & 1), (i >> 1) & 1);
+    const TileMeta* m = L::kMetaRing
+                            ? reinterpret_cast<const TileMeta*>(wsm + L::kOffMetaRing + (i & 1) * kMetaBytes)
+                            : reinterpret_cast<const TileMeta*>(st + L::kOffMeta);
     const int r0 = m->r0, n = m->n, p0 = m->p0;
     const int flags = m->np;
     const int kind = (flags >> kTileKindShift) & 3;  // 0 whole points, 1 / 2 chunk of a long point
@@ -265,13 +306,21 @@ point_stream_kernel(const StreamArgs a) {
       IssueTile<L>(a, t + L::kStages, hnext, st, full + s, stream_policy);
       if (t + L::kStages + 1 < t_end) hnext = LoadHeader(a.tiles + t + L::kStages + 1);
     }
+    // (meta ring) this tile's record is in registers: its slot takes the record two tiles ahead
+    if (L::kMetaRing && lane == 0 && t + 2 < t_end)
+      IssueMeta(a, t + 2, wsm + L::kOffMetaRing + (i & 1) * kMetaBytes, full + L::kStages + (i & 1));
 
     // ---- t = F x; start the gather of the next tile ----
     if (MODE != kModeRhs) {
       if (t + 1 < t_end) {
-        const int s1 = (i + 1) % L::kStages;
-        mbar_wait(full + s1, ((i + 1) / L::kStages) & 1);
-        gather_x(reinterpret_cast<const TileMeta*>(wsm + s1 * L::kStageBytes + L::kOffMeta));
+        if (L::kMetaRing) {
+          mbar_wait(full + L::kStages + ((i + 1) & 1), ((i + 1) >> 1) & 1);
+          gather_x(reinterpret_cast<const TileMeta*>(wsm + L::kOffMetaRing + ((i + 1) & 1) * kMetaBytes));
+        } else {
+          const int s1 = (i + 1) % L::kStages;
+          mbar_wait(full + s1, ((i + 1) / L::kStages) & 1);
+          gather_x(reinterpret_cast<const TileMeta*>(wsm + s1 * L::kStageBytes + L::kOffMeta));
+        }
       }
       double xr[10];
 #pragma unroll
